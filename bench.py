@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""bench.py -- series-windows scored / s on the BASELINE.json headline workload.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (libforemast_gpu)
+    python bench.py --impl reference --steps K --warmup W    # CPU arm (oracle port, all host threads)
+
+Workload (config.workload): per GPU 1,000,000 series-windows x 1440 points (720-point baseline +
+720-point current, BASELINE.json configs[2] shape at the metric's 1440-pt window), all scorers
+enabled: Mann-Whitney + Wilcoxon + Kruskal (ALL), MA band + EWMA + double-exponential bands,
+per-service verdict fold (80 series per service).  Synthetic Philox data.
+A step = one scoring pass over the whole batch.  Weak scaling: every rank scores its own 1M units
+(global unit ids rank*1M...), the only exchange is the per-service counter merge (NCCL all-reduce).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from foremast_b200 import _abi as abi  # noqa: E402
+
+METRIC = "series-windows scored/sec (1440-pt)"
+UNIT = "series-windows/s"
+N_BASE, N_CUR, N_HIST = 720, 720, 0
+UNITS_PER_SERVICE = 80
+ALGS = abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES
+
+
+def workload_name(n_units):
+    return (f"{n_units} series-windows/GPU x 1440 pt (720 baseline + 720 current), all scorers: "
+            "MWU+Wilcoxon+Kruskal (ALL), MA+EWMA+DES bands, verdict fold (80 series/service)")
+
+
+def bench_params(defaults):
+    p = defaults
+    p.algorithms = ALGS
+    p.pairwise = abi.PW_ALL
+    return p
+
+
+def algorithmic_bytes(n_units, n_services):
+    """SURVEY 8(d) per-unit figures x units (DESIGN.md 'Algorithmic bytes')."""
+    n = N_HIST + N_BASE + N_CUR
+    return {
+        "rank": n_units * (4 * (N_BASE + N_CUR) + 8 + 12 + 64),
+        "band": n_units * (4 * n + 8 + 12 + 16),
+        "verdict": n_units * (8 + 4) + n_services * 24,
+    }
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 8 for i in range(4) if r[4 + i].lower() == "active"})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_port_rate(oracle, csr, params, threads):
+    t0 = time.perf_counter()
+    oracle.score(csr, params, threads=threads)
+    sc_t = time.perf_counter() - t0
+    return csr.n_units / sc_t, sc_t
+
+
+def run_reference(args):
+    """Reference arm: the CPU restatement of the brain's pass (oracle 'port'; the reference's own
+    scorer source is not in the mount) on all host threads, same workload shape, bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle
+    threads = oracle.max_threads()
+    sample = args.ref_units
+    csr = oracle.synth(sample, N_HIST, N_BASE, N_CUR, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
+                       flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+    p = bench_params(oracle.params_default())
+    for _ in range(args.warmup):
+        oracle.score(csr, p, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sc, _, _ = oracle.score(csr, p, threads=threads)
+        oracle.verdicts(csr, sc, csr.n_services)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = sample / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(1_000_000), "sample_units_per_step": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"{sample} units of the same workload per step, OpenMP over units"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from foremast_b200 import dist as fdist
+    from foremast_b200.api import Context, default_params
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n = args.units
+    ctx = Context(local)
+    total_services = (n * world + UNITS_PER_SERVICE - 1) // UNITS_PER_SERVICE
+    batch = ctx.batch_synth(n, N_HIST, N_BASE, N_CUR, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
+                            flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, first_unit=rank * n)
+    batch.set_shard(rank * n, total_services)
+    p = bench_params(default_params())
+
+    stage_ms = {"setup": [], "rank": [], "band": [], "verdict": []}
+
+    def step(record):
+        res = ctx.score(batch, p)
+        if world > 1:
+            res.sync()
+            counts, worst = fdist.alias_service_buffers(res)
+            fdist.merge_service_counters(counts, worst)
+            torch.cuda.synchronize()
+        v = res.verdicts()  # finalize kernel + D2H of the per-service verdicts
+        if record:
+            for k, t in res.timings_ms().items():
+                stage_ms[k].append(t)
+        res.free()
+        return v
+
+    for _ in range(args.warmup):
+        step(False)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ctx.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        verdicts = step(True)
+    dev_ms = ctx.timer_stop()
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end through the public one-shot call: pinned host CSR -> H2D -> score -> verdicts D2H
+    host = batch.download()
+    nbytes = host.values.nbytes
+    pinned, pin_ptr = ctx.host_alloc(nbytes)
+    pv = pinned.view(np.float32)
+    pv[:] = host.values
+    host_p = abi.HostCsr.__new__(abi.HostCsr)
+    host_p.values, host_p.offsets, host_p.seg_lens = pv, host.offsets, host.seg_lens
+    host_p.service_id, host_p.metric_type = host.service_id, host.metric_type
+    h2d = pv.nbytes + host.offsets.nbytes + host.seg_lens.nbytes + host.service_id.nbytes + host.metric_type.nbytes
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    ctx.score_host(host_p, p, total_services)  # warm-up
+    barrier()
+    t1 = time.perf_counter()
+    for _ in range(e2e_steps):
+        v2 = ctx.score_host(host_p, p, total_services)
+    barrier()
+    e2e_s = (time.perf_counter() - t1) / e2e_steps
+    if world == 1:
+        assert v2.tobytes() == verdicts.tobytes(), "e2e verdicts differ from the device-resident run"
+
+    t = torch.tensor([dev_ms, wall_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms = (float(x) for x in t.tolist())
+
+    if rank == 0:
+        ms_per_step = dev_ms / args.steps
+        value = n * world / (ms_per_step * 1e-3)
+        peak, peak_src = measured_peak()
+        ab = algorithmic_bytes(n, total_services)
+        avg = {k: (sum(v) / len(v) if v else 0.0) for k, v in stage_ms.items()}
+        kernels = {}
+        for k in ("rank", "band", "verdict"):
+            gbs = ab[k] / (avg[k] * 1e-3) / 1e9 if avg[k] > 0 else 0.0
+            kernels[k] = {"ms": avg[k], "algorithmic_bytes": ab[k], "achieved_gbs": gbs, "frac": gbs / peak}
+        dom = max(("rank", "band", "verdict"), key=lambda k: avg[k])
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get(dom)
+            except Exception:
+                traffic = None
+        # CPU baseline: the oracle port on this box's host cores, bounded sample of the same workload
+        from oracle import oracle
+        threads = oracle.max_threads()
+        sample = min(n, args.cpu_units)
+        stride = int(host.offsets[1])
+        sub = abi.HostCsr(host.values[:sample * stride + 32], host.offsets[:sample + 1], host.seg_lens[:sample],
+                          host.service_id[:sample], host.metric_type[:sample])
+        cpu_rate, cpu_s = cpu_port_rate(oracle, sub, p, threads)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(n), "units_per_gpu": n, "n_services": total_services,
+                       "l2": "inputs (5.76 GB/GPU) larger than L2; no flush needed",
+                       "timing": "CUDA events on the library stream around the K steps, max over ranks",
+                       "wall_ms_per_step": wall_ms / args.steps},
+            "roofline": {"bound": "hbm", "kernel": {"rank": "k_rank", "band": "k_band", "verdict": "k_verdict_reduce"}[dom],
+                         "achieved": kernels[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                         "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
+                         "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0},
+            "kernels": kernels,
+            "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"first {sample} units of rank 0's batch, one pass, {cpu_s:.2f} s"},
+            "e2e": {"value": n * world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps},
+            "gpu_launches": 4 * args.steps + 4 * (e2e_steps + 1) + 1,
+            "clocks": clocks,
+            "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
+                                "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
+        }
+        print(json.dumps(line))
+    ctx.host_free(pin_ptr)
+    batch.free()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--units", type=int, default=1_000_000, help="series-windows per GPU")
+    ap.add_argument("--cpu-units", type=int, default=131072, help="cpu_baseline sample (units)")
+    ap.add_argument("--ref-units", type=int, default=65536, help="--impl reference: units per step")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,202 @@
+"""Object layer over the C ABI: Context / Batch / Result.  Mirrors the order of the brain's
+pass (ingest -> pairwise -> model -> flags -> verdict, docs/guides/design.md:35) and nothing else."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as abi
+from ._lib import ForemastGpuError, load
+
+
+def default_params():
+    p = abi.Params()
+    load().fm_params_default(C.byref(p))
+    return p
+
+
+class Context:
+    def __init__(self, device=-1):
+        self._L = load()
+        self._h = C.c_void_p()
+        rc = self._L.fm_init(C.byref(abi.Config(device, 0)), C.byref(self._h))
+        if rc:
+            raise ForemastGpuError(rc, self._L.fm_strerror(rc).decode())
+
+    def _check(self, rc):
+        if rc:
+            msg = self._L.fm_last_error(self._h).decode() or self._L.fm_strerror(rc).decode()
+            raise ForemastGpuError(rc, msg)
+
+    def close(self):
+        if self._h:
+            self._L.fm_shutdown(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def device_info(self):
+        sm, hbm, name = C.c_int32(), C.c_uint64(), C.create_string_buffer(256)
+        self._check(self._L.fm_device_info(self._h, C.byref(sm), C.byref(hbm), name, 256))
+        return {"sm_count": sm.value, "hbm_bytes": hbm.value, "name": name.value.decode()}
+
+    def timer_start(self):
+        self._check(self._L.fm_timer_start(self._h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self._L.fm_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def host_alloc(self, nbytes):
+        """Pinned host memory as a uint8 numpy array (freed with host_free)."""
+        p = C.c_void_p()
+        self._check(self._L.fm_host_alloc(self._h, nbytes, C.byref(p)))
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint8)
+        arr._fm_ptr = None
+        return arr, p.value
+
+    def host_free(self, ptr):
+        self._L.fm_host_free(self._h, ptr)
+
+    # ---- ingest
+    def batch_from_units(self, units, service_id=None, metric_type=None):
+        """Incremental path (fm_batch_begin / add_series / seal); units = [(hist, base, cur), ...]."""
+        h = C.c_void_p()
+        self._check(self._L.fm_batch_begin(self._h, len(units), sum(len(a) + len(b) + len(c) for a, b, c in units), C.byref(h)))
+        b = Batch(self, h)
+        for i, (hist, base, cur) in enumerate(units):
+            arrs = [np.ascontiguousarray(x, dtype=np.float32) for x in (hist, base, cur)]
+            meta = abi.SeriesMeta(int(service_id[i]) if service_id is not None else 0,
+                                  int(metric_type[i]) if metric_type is not None else 0)
+            self._check(self._L.fm_batch_add_series(
+                h, C.byref(meta), arrs[0].ctypes.data, arrs[0].size, arrs[1].ctypes.data, arrs[1].size,
+                arrs[2].ctypes.data, arrs[2].size))
+        self._check(self._L.fm_batch_seal(h))
+        return b
+
+    def batch_from_csr(self, csr):
+        h = C.c_void_p()
+        st = csr.as_struct()
+        self._check(self._L.fm_batch_from_csr(self._h, C.byref(st), C.byref(h)))
+        return Batch(self, h)
+
+    def batch_from_device(self, n_units, values_ptr, offsets_ptr, seg_ptr, sid_ptr, mt_ptr, keepalive=None):
+        h = C.c_void_p()
+        st = abi.Csr(n_units, values_ptr, offsets_ptr, seg_ptr, sid_ptr, mt_ptr)
+        self._check(self._L.fm_batch_from_device(self._h, C.byref(st), C.byref(h)))
+        b = Batch(self, h)
+        b._keepalive = keepalive
+        return b
+
+    def batch_synth(self, n_units, n_hist, n_base, n_cur, units_per_service=80, n_metric_types=8,
+                    seed=0xF03E5A57, flags=0, first_unit=0):
+        cfg = abi.SynthConfig(n_units, n_hist, n_base, n_cur, units_per_service, n_metric_types,
+                              seed & 0xFFFFFFFF, flags, 0, first_unit)
+        h = C.c_void_p()
+        self._check(self._L.fm_batch_synth(self._h, C.byref(cfg), C.byref(h)))
+        return Batch(self, h)
+
+    def score(self, batch, params):
+        h = C.c_void_p()
+        self._check(self._L.fm_score(self._h, batch._h, C.byref(params), C.byref(h)))
+        return Result(self, batch, h)
+
+    def score_host(self, csr, params, n_services=None):
+        """One-shot host-in / host-out call (fm_score_host): returns VERDICT array."""
+        ns = csr.n_services if n_services is None else n_services
+        out = np.zeros(ns, dtype=abi.VERDICT)
+        st = csr.as_struct()
+        self._check(self._L.fm_score_host(self._h, C.byref(st), C.byref(params), ns, out.ctypes.data))
+        return out
+
+
+class Batch:
+    def __init__(self, ctx, handle):
+        self.ctx, self._h, self._keepalive = ctx, handle, None
+
+    def info(self):
+        n, nv, ns = C.c_uint64(), C.c_uint64(), C.c_uint32()
+        self.ctx._check(self.ctx._L.fm_batch_info(self._h, C.byref(n), C.byref(nv), C.byref(ns)))
+        return {"n_units": n.value, "n_values": nv.value, "n_services": ns.value}
+
+    def set_shard(self, first_unit, n_services):
+        self.ctx._check(self.ctx._L.fm_batch_set_shard(self._h, first_unit, n_services))
+
+    def download(self):
+        """Packed CSR back on the host (tests and the CPU baseline read the same inputs)."""
+        i = self.info()
+        n = i["n_units"]
+        values = np.empty(i["n_values"], np.float32)
+        offsets = np.empty(n + 1, np.int64)
+        seg = np.empty((n, 3), np.uint32)
+        sid = np.empty(n, np.uint32)
+        mt = np.empty(n, np.uint8)
+        self.ctx._check(self.ctx._L.fm_batch_download(
+            self._h, values.ctypes.data, offsets.ctypes.data, seg.ctypes.data, sid.ctypes.data, mt.ctypes.data))
+        return abi.HostCsr(values, offsets, seg, sid, mt)
+
+    def free(self):
+        if self._h:
+            self.ctx._L.fm_batch_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Result:
+    def __init__(self, ctx, batch, handle):
+        self.ctx, self.batch, self._h = ctx, batch, handle
+
+    def sync(self):
+        self.ctx._check(self.ctx._L.fm_result_sync(self._h))
+
+    def verdicts(self):
+        ns = self.batch.info()["n_services"]
+        out = np.zeros(ns, dtype=abi.VERDICT)
+        n = C.c_uint64()
+        self.ctx._check(self.ctx._L.fm_result_verdicts(self._h, out.ctypes.data, ns, C.byref(n)))
+        return out
+
+    def series(self, first=0, count=None):
+        n = self.batch.info()["n_units"]
+        count = n - first if count is None else count
+        out = np.zeros(count, dtype=abi.SERIES_SCORE)
+        self.ctx._check(self.ctx._L.fm_result_series(self._h, first, count, out.ctypes.data))
+        return out
+
+    def bands(self, unit, cap=1 << 16):
+        up = np.empty(cap, np.float32)
+        lo = np.empty(cap, np.float32)
+        n = C.c_uint32()
+        self.ctx._check(self.ctx._L.fm_result_bands(self._h, unit, up.ctypes.data, lo.ctypes.data, cap, C.byref(n)))
+        return up[:n.value].copy(), lo[:n.value].copy()
+
+    def service_buffers(self):
+        counts, worst, ns = C.c_void_p(), C.c_void_p(), C.c_uint32()
+        self.ctx._check(self.ctx._L.fm_result_service_buffers(self._h, C.byref(counts), C.byref(worst), C.byref(ns)))
+        return counts.value, worst.value, ns.value
+
+    def timings_ms(self):
+        ms = (C.c_float * 4)()
+        self.ctx._check(self.ctx._L.fm_result_timings(self._h, ms, 4))
+        return {"setup": ms[0], "rank": ms[1], "band": ms[2], "verdict": ms[3]}
+
+    def free(self):
+        if self._h:
+            self.ctx._L.fm_result_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

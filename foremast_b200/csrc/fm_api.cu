@@ -1,0 +1,730 @@
+// fm_api.cu -- the C ABI of libforemast_gpu (include/foremast_gpu.h): contexts, ingest into the
+// ragged CSR layout in HBM, the scoring pass, result accessors.  No torch types, no exceptions
+// across the edge, no CPU scoring path: every score comes from the kernels in this directory.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "fm_common.cuh"
+
+// ------------------------------------------------------------------ objects
+
+struct fm_ctx {
+  int device = 0;
+  int sm_count = 0;
+  uint64_t hbm_bytes = 0;
+  char name[256] = {0};
+  cudaStream_t stream = nullptr;       // compute
+  cudaStream_t copy_stream = nullptr;  // H2D staging of fm_score_host
+  cudaEvent_t timer[2] = {nullptr, nullptr};
+  std::mutex mu;
+  std::string last_error;
+};
+
+struct fm_batch {
+  fm_ctx *ctx = nullptr;
+  bool sealed = false, owns = true;
+  uint64_t n_units = 0, n_values = 0;  // n_values: allocated elements incl. 32 pad
+  uint32_t n_services = 0, max_hist = 0, max_base = 0, max_cur = 0;
+  uint64_t first_unit = 0;
+  float *d_values = nullptr;
+  int64_t *d_offsets = nullptr;
+  uint32_t *d_seg = nullptr, *d_sid = nullptr;
+  uint8_t *d_mt = nullptr;
+  // host staging of the incremental path
+  std::vector<float> h_values;
+  std::vector<int64_t> h_offsets;
+  std::vector<uint32_t> h_seg, h_sid;
+  std::vector<uint8_t> h_mt;
+};
+
+struct fm_result {
+  fm_ctx *ctx = nullptr;
+  const fm_batch *batch = nullptr;
+  uint64_t n_units = 0;
+  uint32_t n_services = 0;
+  uint32_t band_algorithm = 0;
+  DevParams *d_params = nullptr;
+  fm_series_score *d_scores = nullptr;
+  uint32_t *d_unit_status = nullptr, *d_unit_points = nullptr, *d_counts = nullptr;
+  unsigned long long *d_worst = nullptr;
+  fm_verdict *d_verdicts = nullptr;
+  float *d_band_up = nullptr, *d_band_lo = nullptr;
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // start, pre-rank, post-rank, post-band, post-verdict
+};
+
+namespace {
+
+int set_err(fm_ctx *ctx, int code, const std::string &msg) {
+  if (ctx) ctx->last_error = msg;
+  return code;
+}
+
+#define FM_CUDA(ctx, expr)                                                                      \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      cudaGetLastError();                                                                       \
+      return set_err((ctx), _e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,           \
+                     std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
+    }                                                                                           \
+  } while (0)
+
+DevBatch dev_view(const fm_batch *b) {
+  DevBatch d;
+  d.n_units = b->n_units;
+  d.values = b->d_values;
+  d.offsets = b->d_offsets;
+  d.seg_lens = b->d_seg;
+  d.service_id = b->d_sid;
+  d.metric_type = b->d_mt;
+  d.first_unit = b->first_unit;
+  return d;
+}
+
+void resolve_params(const fm_params *p, DevParams *d) {
+  memset(d, 0, sizeof(*d));
+  d->algorithms = p->algorithms;
+  d->pairwise = p->pairwise;
+  d->pairwise_threshold = p->pairwise_threshold;
+  d->differ_scale = p->differ_scale;
+  d->min_mann_white = p->min_mann_white;
+  d->min_wilcoxon = p->min_wilcoxon;
+  d->min_kruskal = p->min_kruskal;
+  d->min_historical = p->min_historical;
+  d->min_anomaly_points = p->min_anomaly_points;
+  d->ma_window = p->ma_window ? p->ma_window : 1;
+  d->period = p->period;
+  d->band_algorithm = p->band_algorithm;
+  d->alpha = p->alpha;
+  d->beta = p->beta;
+  d->gamma = p->gamma;
+  for (int i = 0; i < FM_MAX_METRIC_TYPES; ++i) {
+    const fm_metric_rule &r = p->rules[i].bound ? p->rules[i] : p->rules[0];  // D16
+    d->rules[i].threshold = r.threshold;
+    d->rules[i].min_lower_bound = r.min_lower_bound;
+    d->rules[i].bound = r.bound;
+  }
+}
+
+int alloc_device_csr(fm_batch *b, uint64_t n_units, uint64_t n_values) {
+  fm_ctx *ctx = b->ctx;
+  FM_CUDA(ctx, cudaMalloc(&b->d_values, n_values * sizeof(float)));
+  FM_CUDA(ctx, cudaMalloc(&b->d_offsets, (n_units + 1) * sizeof(int64_t)));
+  FM_CUDA(ctx, cudaMalloc(&b->d_seg, (3 * n_units + 1) * sizeof(uint32_t)));
+  FM_CUDA(ctx, cudaMalloc(&b->d_sid, (n_units + 1) * sizeof(uint32_t)));
+  FM_CUDA(ctx, cudaMalloc(&b->d_mt, n_units + 1));
+  b->n_units = n_units;
+  b->n_values = n_values;
+  return FM_OK;
+}
+
+// upload a host CSR whose offsets are already multiples of 4
+int upload_aligned(fm_batch *b, const fm_csr *h, uint64_t used) {
+  fm_ctx *ctx = b->ctx;
+  const uint64_t n = h->n_units;
+  int rc = alloc_device_csr(b, n, used + 32);
+  if (rc) return rc;
+  cudaStream_t st = ctx->stream;
+  if (used) FM_CUDA(ctx, cudaMemcpyAsync(b->d_values, h->values, used * sizeof(float), cudaMemcpyHostToDevice, st));
+  FM_CUDA(ctx, cudaMemsetAsync(b->d_values + used, 0, 32 * sizeof(float), st));
+  FM_CUDA(ctx, cudaMemcpyAsync(b->d_offsets, h->offsets, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  if (n) {
+    FM_CUDA(ctx, cudaMemcpyAsync(b->d_seg, h->seg_lens, 3 * n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    if (h->service_id)
+      FM_CUDA(ctx, cudaMemcpyAsync(b->d_sid, h->service_id, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    else
+      FM_CUDA(ctx, cudaMemsetAsync(b->d_sid, 0, n * sizeof(uint32_t), st));
+    if (h->metric_type)
+      FM_CUDA(ctx, cudaMemcpyAsync(b->d_mt, h->metric_type, n, cudaMemcpyHostToDevice, st));
+    else
+      FM_CUDA(ctx, cudaMemsetAsync(b->d_mt, 0, n, st));
+  }
+  FM_CUDA(ctx, cudaStreamSynchronize(st));  // inputs are borrowed for the call only
+  return FM_OK;
+}
+
+// host-side scan of a CSR: validity, alignment, maxima
+int scan_host_csr(fm_ctx *ctx, const fm_csr *h, bool *aligned, uint64_t *used, fm_batch *b) {
+  *aligned = true;
+  uint32_t mh = 0, mb = 0, mc = 0, ms = 0;
+  for (uint64_t u = 0; u < h->n_units; ++u) {
+    const int64_t o = h->offsets[u], o1 = h->offsets[u + 1];
+    const uint64_t len = (uint64_t)h->seg_lens[3 * u] + h->seg_lens[3 * u + 1] + h->seg_lens[3 * u + 2];
+    if (o < 0 || o1 < o || (uint64_t)(o1 - o) < len) return set_err(ctx, FM_E_INVALID, "CSR offsets inconsistent with seg_lens");
+    if (o & 3) *aligned = false;
+    mh = std::max(mh, h->seg_lens[3 * u]);
+    mb = std::max(mb, h->seg_lens[3 * u + 1]);
+    mc = std::max(mc, h->seg_lens[3 * u + 2]);
+    if (h->service_id) ms = std::max(ms, h->service_id[u]);
+  }
+  *used = h->n_units ? (uint64_t)h->offsets[h->n_units] : 0;
+  if (h->n_units && (h->offsets[h->n_units] & 3)) *used = (*used + 3) & ~3ull;
+  b->max_hist = mh; b->max_base = mb; b->max_cur = mc;
+  b->n_services = h->n_units ? ms + 1 : 0;
+  return FM_OK;
+}
+
+void free_batch_device(fm_batch *b) {
+  if (b->owns) {
+    cudaFree(b->d_values); cudaFree(b->d_offsets); cudaFree(b->d_seg); cudaFree(b->d_sid); cudaFree(b->d_mt);
+  }
+  b->d_values = nullptr; b->d_offsets = nullptr; b->d_seg = nullptr; b->d_sid = nullptr; b->d_mt = nullptr;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ life cycle
+
+extern "C" {
+
+int fm_version(void) { return FM_ABI_VERSION; }
+
+const char *fm_strerror(int code) {
+  switch (code) {
+    case FM_OK: return "ok";
+    case FM_E_INVALID: return "invalid argument";
+    case FM_E_NOMEM: return "out of memory";
+    case FM_E_CUDA: return "CUDA error";
+    case FM_E_NO_DEVICE: return "no sm_100 GPU available (libforemast_gpu has no CPU path)";
+    case FM_E_ALIGN: return "device CSR offsets must be multiples of 4 elements and values 16-byte aligned";
+    case FM_E_STATE: return "call order violated";
+    case FM_E_RANGE: return "index or size out of range";
+    case FM_E_UNSUPPORTED: return "unsupported request";
+    case FM_E_COMM: return "multi-GPU exchange failed";
+    default: return "unknown error";
+  }
+}
+
+const char *fm_last_error(const fm_ctx *ctx) { return ctx ? ctx->last_error.c_str() : "no context"; }
+
+// Documented defaults: deploy/foremast/3_brain/foremast-brain.yaml:24-79; the rest oracle/DECISIONS.md.
+void fm_params_default(fm_params *p) {
+  if (!p) return;
+  memset(p, 0, sizeof(*p));
+  p->algorithms = FM_ALG_MA_ALL;
+  p->pairwise = FM_PW_ALL;
+  p->pairwise_threshold = 0.05;
+  p->differ_scale = 0.5;
+  p->min_mann_white = 20;
+  p->min_wilcoxon = 20;
+  p->min_kruskal = 5;
+  p->min_historical = 10;
+  p->min_anomaly_points = 1;
+  p->ma_window = 30;
+  p->period = 1440;
+  p->alpha = 0.3;
+  p->beta = 0.1;
+  p->gamma = 0.1;
+  p->rules[FM_MT_OTHER] = fm_metric_rule{2.0, 0.0, FM_BOUND_UPPER, 0};
+  p->rules[FM_MT_ERROR5XX] = fm_metric_rule{2.0, 0.0, FM_BOUND_UPPER, 0};
+  p->rules[FM_MT_ERROR4XX] = fm_metric_rule{3.0, 0.0, FM_BOUND_UPPER, 0};
+  p->rules[FM_MT_LATENCY] = fm_metric_rule{10.0, 0.0, FM_BOUND_BOTH, 0};
+  p->rules[FM_MT_CPU] = fm_metric_rule{5.0, 0.0, FM_BOUND_UPPER, 0};
+  p->rules[FM_MT_MEMORY] = fm_metric_rule{5.0, 0.0, FM_BOUND_UPPER, 0};
+}
+
+int fm_init(const fm_config *cfg, fm_ctx **out) {
+  if (!out) return FM_E_INVALID;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return FM_E_NO_DEVICE;
+  }
+  int dev = cfg ? cfg->device : -1;
+  if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return FM_E_NO_DEVICE;
+  if (dev >= count) return FM_E_NO_DEVICE;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return FM_E_NO_DEVICE;
+  if (prop.major != 10) return FM_E_NO_DEVICE;  // kernels are built for sm_100a only
+  fm_ctx *ctx = new (std::nothrow) fm_ctx;
+  if (!ctx) return FM_E_NOMEM;
+  ctx->device = dev;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->hbm_bytes = prop.totalGlobalMem;
+  snprintf(ctx->name, sizeof(ctx->name), "%s", prop.name);
+  if (cudaSetDevice(dev) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return FM_E_CUDA;
+  }
+  // keep freed result buffers in the stream-ordered pool: steady-state fm_score allocates nothing new
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    uint64_t thresh = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh);
+  }
+  *out = ctx;
+  return FM_OK;
+}
+
+void fm_shutdown(fm_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto &e : ctx->timer)
+    if (e) cudaEventDestroy(e);
+  cudaStreamDestroy(ctx->stream);
+  cudaStreamDestroy(ctx->copy_stream);
+  delete ctx;
+}
+
+int fm_device_info(const fm_ctx *ctx, int32_t *sm_count, uint64_t *hbm_bytes, char *name, uint32_t name_cap) {
+  if (!ctx) return FM_E_INVALID;
+  if (sm_count) *sm_count = ctx->sm_count;
+  if (hbm_bytes) *hbm_bytes = ctx->hbm_bytes;
+  if (name && name_cap) snprintf(name, name_cap, "%s", ctx->name);
+  return FM_OK;
+}
+
+int fm_timer_start(fm_ctx *ctx) {
+  if (!ctx) return FM_E_INVALID;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  for (auto &e : ctx->timer)
+    if (!e) FM_CUDA(ctx, cudaEventCreate(&e));
+  FM_CUDA(ctx, cudaEventRecord(ctx->timer[0], ctx->stream));
+  return FM_OK;
+}
+
+int fm_timer_stop(fm_ctx *ctx, float *ms) {
+  if (!ctx || !ms || !ctx->timer[0]) return FM_E_INVALID;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  FM_CUDA(ctx, cudaEventRecord(ctx->timer[1], ctx->stream));
+  FM_CUDA(ctx, cudaEventSynchronize(ctx->timer[1]));
+  FM_CUDA(ctx, cudaEventElapsedTime(ms, ctx->timer[0], ctx->timer[1]));
+  return FM_OK;
+}
+
+int fm_host_alloc(fm_ctx *ctx, uint64_t bytes, void **out) {
+  if (!ctx || !out) return FM_E_INVALID;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  FM_CUDA(ctx, cudaMallocHost(out, bytes ? bytes : 1));
+  return FM_OK;
+}
+
+void fm_host_free(fm_ctx *ctx, void *p) {
+  if (!ctx || !p) return;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  cudaSetDevice(ctx->device);
+  cudaFreeHost(p);
+}
+
+// ------------------------------------------------------------------ ingest
+
+int fm_batch_begin(fm_ctx *ctx, uint64_t n_units_hint, uint64_t n_points_hint, fm_batch **out) {
+  if (!ctx || !out) return FM_E_INVALID;
+  fm_batch *b = new (std::nothrow) fm_batch;
+  if (!b) return FM_E_NOMEM;
+  b->ctx = ctx;
+  try {
+    b->h_values.reserve(n_points_hint + 4 * n_units_hint + 32);
+    b->h_offsets.reserve(n_units_hint + 1);
+    b->h_seg.reserve(3 * n_units_hint);
+    b->h_sid.reserve(n_units_hint);
+    b->h_mt.reserve(n_units_hint);
+  } catch (...) {
+    delete b;
+    return FM_E_NOMEM;
+  }
+  *out = b;
+  return FM_OK;
+}
+
+int fm_batch_add_series(fm_batch *b, const fm_series_meta *meta, const float *hist, uint32_t n_hist,
+                        const float *base, uint32_t n_base, const float *cur, uint32_t n_cur) {
+  if (!b || !meta || (n_hist && !hist) || (n_base && !base) || (n_cur && !cur)) return FM_E_INVALID;
+  if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
+  try {
+    b->h_offsets.push_back((int64_t)b->h_values.size());
+    const float *seg[3] = {hist, base, cur};
+    const uint32_t len[3] = {n_hist, n_base, n_cur};
+    for (int s = 0; s < 3; ++s) {
+      uint32_t kept = 0;
+      for (uint32_t i = 0; i < len[s]; ++i) {
+        const float x = seg[s][i];
+        if (!std::isfinite(x)) continue;       // a gap (D11)
+        b->h_values.push_back(x + 0.0f);       // -0.0 -> +0.0
+        ++kept;
+      }
+      b->h_seg.push_back(kept);
+    }
+    while (b->h_values.size() & 3) b->h_values.push_back(0.0f);
+    b->h_sid.push_back(meta->service_id);
+    b->h_mt.push_back(meta->metric_type);
+  } catch (...) {
+    return set_err(b->ctx, FM_E_NOMEM, "host staging allocation failed");
+  }
+  return FM_OK;
+}
+
+int fm_batch_seal(fm_batch *b) {
+  if (!b) return FM_E_INVALID;
+  if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
+  fm_ctx *ctx = b->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  b->h_offsets.push_back((int64_t)b->h_values.size());
+  fm_csr h;
+  h.n_units = b->h_sid.size();
+  h.values = b->h_values.data();
+  h.offsets = b->h_offsets.data();
+  h.seg_lens = b->h_seg.data();
+  h.service_id = b->h_sid.data();
+  h.metric_type = b->h_mt.data();
+  bool aligned;
+  uint64_t used;
+  int rc = scan_host_csr(ctx, &h, &aligned, &used, b);
+  if (rc) return rc;
+  rc = upload_aligned(b, &h, used);
+  if (rc) { free_batch_device(b); return rc; }
+  b->sealed = true;
+  std::vector<float>().swap(b->h_values);
+  return FM_OK;
+}
+
+int fm_batch_from_csr(fm_ctx *ctx, const fm_csr *h, fm_batch **out) {
+  if (!ctx || !h || !out || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return FM_E_INVALID;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  fm_batch *b = new (std::nothrow) fm_batch;
+  if (!b) return FM_E_NOMEM;
+  b->ctx = ctx;
+  bool aligned;
+  uint64_t used;
+  int rc = scan_host_csr(ctx, h, &aligned, &used, b);
+  if (rc == FM_OK) {
+    if (aligned) {
+      rc = upload_aligned(b, h, h->n_units ? (uint64_t)h->offsets[h->n_units] : 0);
+    } else {  // re-pack so that every unit starts on a 16-byte boundary
+      try {
+        std::vector<float> v;
+        std::vector<int64_t> o(h->n_units + 1);
+        v.reserve(used + 4 * h->n_units);
+        for (uint64_t u = 0; u < h->n_units; ++u) {
+          o[u] = (int64_t)v.size();
+          const uint64_t len = (uint64_t)h->seg_lens[3 * u] + h->seg_lens[3 * u + 1] + h->seg_lens[3 * u + 2];
+          v.insert(v.end(), h->values + h->offsets[u], h->values + h->offsets[u] + len);
+          while (v.size() & 3) v.push_back(0.0f);
+        }
+        o[h->n_units] = (int64_t)v.size();
+        fm_csr h2 = *h;
+        h2.values = v.data();
+        h2.offsets = o.data();
+        rc = upload_aligned(b, &h2, v.size());
+      } catch (...) {
+        rc = set_err(ctx, FM_E_NOMEM, "host re-pack allocation failed");
+      }
+    }
+  }
+  if (rc) { free_batch_device(b); delete b; return rc; }
+  b->sealed = true;
+  *out = b;
+  return FM_OK;
+}
+
+int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
+  if (!ctx || !d || !out || !d->values || !d->offsets || !d->seg_lens || !d->service_id || !d->metric_type) return FM_E_INVALID;
+  if (reinterpret_cast<uintptr_t>(d->values) & 15) return set_err(ctx, FM_E_ALIGN, "values pointer is not 16-byte aligned");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  fm_batch *b = new (std::nothrow) fm_batch;
+  if (!b) return FM_E_NOMEM;
+  b->ctx = ctx;
+  b->owns = false;
+  b->n_units = d->n_units;
+  b->d_values = const_cast<float *>(d->values);
+  b->d_offsets = const_cast<int64_t *>(d->offsets);
+  b->d_seg = const_cast<uint32_t *>(d->seg_lens);
+  b->d_sid = const_cast<uint32_t *>(d->service_id);
+  b->d_mt = const_cast<uint8_t *>(d->metric_type);
+  uint32_t *d_stats = nullptr, h_stats[6] = {0, 0, 0, 0, 0, 0};
+  cudaError_t e = cudaMallocAsync(&d_stats, sizeof(h_stats), ctx->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_stats, 0, sizeof(h_stats), ctx->stream);
+  if (e == cudaSuccess) {
+    fm_launch_batch_stats(dev_view(b), d_stats, ctx->stream);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(h_stats, d_stats, sizeof(h_stats), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (d_stats) cudaFreeAsync(d_stats, ctx->stream);
+  if (e != cudaSuccess) {
+    delete b;
+    cudaGetLastError();
+    return set_err(ctx, FM_E_CUDA, std::string("batch statistics: ") + cudaGetErrorString(e));
+  }
+  if (h_stats[4]) { delete b; return set_err(ctx, FM_E_ALIGN, "device CSR offsets must be multiples of 4 elements"); }
+  if (h_stats[5]) { delete b; return set_err(ctx, FM_E_INVALID, "device CSR units overlap"); }
+  b->max_hist = h_stats[0]; b->max_base = h_stats[1]; b->max_cur = h_stats[2];
+  b->n_services = d->n_units ? h_stats[3] + 1 : 0;
+  b->sealed = true;
+  *out = b;
+  return FM_OK;
+}
+
+int fm_batch_synth(fm_ctx *ctx, const fm_synth_config *cfg, fm_batch **out) {
+  if (!ctx || !cfg || !out || cfg->n_metric_types == 0 || cfg->n_metric_types > 8 || cfg->units_per_service == 0) return FM_E_INVALID;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  fm_batch *b = new (std::nothrow) fm_batch;
+  if (!b) return FM_E_NOMEM;
+  b->ctx = ctx;
+  const uint64_t stride = ((uint64_t)cfg->n_hist + cfg->n_base + cfg->n_cur + 3) & ~3ull;
+  int rc = alloc_device_csr(b, cfg->n_units, cfg->n_units * stride + 32);
+  if (rc) { free_batch_device(b); delete b; return rc; }
+  fm_launch_synth(*cfg, stride, b->d_values, b->d_offsets, b->d_seg, b->d_sid, b->d_mt, ctx->stream);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    free_batch_device(b); delete b;
+    cudaGetLastError();
+    return set_err(ctx, FM_E_CUDA, std::string("synthetic generator: ") + cudaGetErrorString(e));
+  }
+  b->max_hist = cfg->n_hist; b->max_base = cfg->n_base; b->max_cur = cfg->n_cur;
+  b->first_unit = cfg->first_unit;
+  b->n_services = cfg->n_units ? (uint32_t)((cfg->first_unit + cfg->n_units - 1) / cfg->units_per_service) + 1 : 0;
+  b->sealed = true;
+  *out = b;
+  return FM_OK;
+}
+
+int fm_batch_set_shard(fm_batch *b, uint64_t first_unit, uint32_t n_services) {
+  if (!b) return FM_E_INVALID;
+  if (n_services < b->n_services) return set_err(b->ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1");
+  b->first_unit = first_unit;
+  b->n_services = n_services;
+  return FM_OK;
+}
+
+int fm_batch_info(const fm_batch *b, uint64_t *n_units, uint64_t *n_values, uint32_t *n_services) {
+  if (!b) return FM_E_INVALID;
+  if (n_units) *n_units = b->n_units;
+  if (n_values) *n_values = b->n_values;
+  if (n_services) *n_services = b->n_services;
+  return FM_OK;
+}
+
+int fm_batch_download(const fm_batch *b, float *values, int64_t *offsets, uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type) {
+  if (!b || !b->sealed) return FM_E_INVALID;
+  fm_ctx *ctx = b->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint64_t n = b->n_units;
+  if (values && b->n_values) FM_CUDA(ctx, cudaMemcpy(values, b->d_values, b->n_values * sizeof(float), cudaMemcpyDeviceToHost));
+  if (offsets) FM_CUDA(ctx, cudaMemcpy(offsets, b->d_offsets, (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  if (seg_lens && n) FM_CUDA(ctx, cudaMemcpy(seg_lens, b->d_seg, 3 * n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  if (service_id && n) FM_CUDA(ctx, cudaMemcpy(service_id, b->d_sid, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  if (metric_type && n) FM_CUDA(ctx, cudaMemcpy(metric_type, b->d_mt, n, cudaMemcpyDeviceToHost));
+  return FM_OK;
+}
+
+void fm_batch_free(fm_batch *b) {
+  if (!b) return;
+  if (b->ctx) {
+    std::lock_guard<std::mutex> g(b->ctx->mu);
+    cudaSetDevice(b->ctx->device);
+    cudaStreamSynchronize(b->ctx->stream);
+    free_batch_device(b);
+  }
+  delete b;
+}
+
+// ------------------------------------------------------------------ scoring
+
+static void result_release(fm_result *r) {
+  cudaStream_t st = r->ctx->stream;
+  void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts,
+                  r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo};
+  for (void *p : ptrs)
+    if (p) cudaFreeAsync(p, st);
+  for (auto &e : r->ev)
+    if (e) cudaEventDestroy(e);
+  delete r;
+}
+
+static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
+  if (p->algorithms & ~FM_ALG_ALL) return set_err(ctx, FM_E_INVALID, "unknown algorithm bits");
+  if (p->algorithms & (FM_ALG_MA_ROLLING | FM_ALG_HW))
+    return set_err(ctx, FM_E_UNSUPPORTED, "FM_ALG_MA_ROLLING / FM_ALG_HW are not built yet");
+  if (p->pairwise > FM_PW_KRUSKAL) return set_err(ctx, FM_E_INVALID, "unknown pairwise algorithm");
+  if (p->band_algorithm && (!(p->band_algorithm & p->algorithms) || (p->band_algorithm & (p->band_algorithm - 1))))
+    return set_err(ctx, FM_E_INVALID, "band_algorithm must be one enabled FM_ALG_* bit");
+  const bool do_rank = p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0;
+  if (do_rank && std::max(b->max_base, b->max_cur) > 1024)
+    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 1024 samples");
+
+  fm_result *r = new (std::nothrow) fm_result;
+  if (!r) return FM_E_NOMEM;
+  r->ctx = ctx;
+  r->batch = b;
+  r->n_units = b->n_units;
+  r->n_services = b->n_services;
+  r->band_algorithm = p->band_algorithm;
+  cudaStream_t st = ctx->stream;
+  const uint64_t n = b->n_units, ns = b->n_services;
+#define FM_R(expr)                                                                              \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      cudaGetLastError();                                                                       \
+      result_release(r);                                                                        \
+      return set_err(ctx, _e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,             \
+                     std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
+    }                                                                                           \
+  } while (0)
+  for (auto &e : r->ev) FM_R(cudaEventCreate(&e));
+  FM_R(cudaMallocAsync(&r->d_params, sizeof(DevParams), st));
+  FM_R(cudaMallocAsync(&r->d_scores, (n + 1) * sizeof(fm_series_score), st));
+  FM_R(cudaMallocAsync(&r->d_unit_status, (n + 1) * sizeof(uint32_t), st));
+  FM_R(cudaMallocAsync(&r->d_unit_points, (n + 1) * sizeof(uint32_t), st));
+  FM_R(cudaMallocAsync(&r->d_counts, (4 * ns + 4) * sizeof(uint32_t), st));
+  FM_R(cudaMallocAsync(&r->d_worst, (ns + 1) * sizeof(unsigned long long), st));
+  FM_R(cudaMallocAsync(&r->d_verdicts, (ns + 1) * sizeof(fm_verdict), st));
+  if (p->band_algorithm) {
+    FM_R(cudaMallocAsync(&r->d_band_up, b->n_values * sizeof(float), st));
+    FM_R(cudaMallocAsync(&r->d_band_lo, b->n_values * sizeof(float), st));
+  }
+  FM_R(cudaEventRecord(r->ev[0], st));
+  DevParams hp;
+  resolve_params(p, &hp);
+  FM_R(cudaMemcpyAsync(r->d_params, &hp, sizeof(hp), cudaMemcpyHostToDevice, st));  // pageable: staged before return
+  FM_R(cudaMemsetAsync(r->d_scores, 0, (n + 1) * sizeof(fm_series_score), st));
+  FM_R(cudaMemsetAsync(r->d_counts, 0, (4 * ns + 4) * sizeof(uint32_t), st));
+  FM_R(cudaMemsetAsync(r->d_worst, 0, (ns + 1) * sizeof(unsigned long long), st));
+
+  const DevBatch db = dev_view(b);
+  FM_R(cudaEventRecord(r->ev[1], st));
+  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, std::max(b->max_base, b->max_cur), r->d_scores, ctx->sm_count, st));
+  FM_R(cudaEventRecord(r->ev[2], st));
+  FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, r->d_scores, r->d_unit_status, r->d_unit_points,
+                      r->d_band_up, r->d_band_lo, st));
+  FM_R(cudaEventRecord(r->ev[3], st));
+  fm_launch_verdict_reduce(db, r->d_unit_status, r->d_unit_points, (uint32_t)ns, r->d_counts, r->d_worst, st);
+  FM_R(cudaGetLastError());
+  FM_R(cudaEventRecord(r->ev[4], st));
+#undef FM_R
+  *out = r;
+  return FM_OK;
+}
+
+int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
+  if (!ctx || !b || !p || !out) return FM_E_INVALID;
+  if (!b->sealed) return set_err(ctx, FM_E_STATE, "batch is not sealed");
+  if (b->ctx != ctx) return set_err(ctx, FM_E_INVALID, "batch belongs to another context");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  return score_locked(ctx, b, p, out);
+}
+
+int fm_result_sync(fm_result *r) {
+  if (!r) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FM_OK;
+}
+
+int fm_result_verdicts(fm_result *r, fm_verdict *out, uint64_t cap, uint64_t *n) {
+  if (!r || !out) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (n) *n = r->n_services;
+  if (cap < r->n_services) return set_err(ctx, FM_E_RANGE, "verdict buffer too small");
+  if (r->n_services == 0) return FM_OK;
+  // finalised at read time so that a cross-GPU merge of the counters can happen in between
+  fm_launch_verdict_finalize(r->n_services, r->d_counts, r->d_worst, r->d_verdicts, ctx->stream);
+  FM_CUDA(ctx, cudaGetLastError());
+  FM_CUDA(ctx, cudaMemcpyAsync(out, r->d_verdicts, r->n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FM_OK;
+}
+
+int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_series_score *out) {
+  if (!r || (!out && count)) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  if (first_unit > r->n_units || count > r->n_units - first_unit) return set_err(ctx, FM_E_RANGE, "unit range outside the batch");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (count)
+    FM_CUDA(ctx, cudaMemcpyAsync(out, r->d_scores + first_unit, count * sizeof(fm_series_score), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FM_OK;
+}
+
+int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uint32_t cap, uint32_t *n) {
+  if (!r || !upper || !lower) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  if (!r->d_band_up) return set_err(ctx, FM_E_STATE, "bands were not requested (params.band_algorithm == 0)");
+  if (unit >= r->n_units) return set_err(ctx, FM_E_RANGE, "unit outside the batch");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int64_t off;
+  uint32_t seg[3];
+  FM_CUDA(ctx, cudaMemcpyAsync(&off, r->batch->d_offsets + unit, sizeof(off), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaMemcpyAsync(seg, r->batch->d_seg + 3 * unit, sizeof(seg), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (n) *n = seg[2];
+  if (cap < seg[2]) return set_err(ctx, FM_E_RANGE, "band buffer too small");
+  const int64_t c0 = off + seg[0] + seg[1];
+  if (seg[2]) {
+    FM_CUDA(ctx, cudaMemcpyAsync(upper, r->d_band_up + c0, seg[2] * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    FM_CUDA(ctx, cudaMemcpyAsync(lower, r->d_band_lo + c0, seg[2] * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return FM_OK;
+}
+
+int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst, uint32_t *n_services) {
+  if (!r) return FM_E_INVALID;
+  if (counts) *counts = r->d_counts;
+  if (worst) *worst = reinterpret_cast<uint64_t *>(r->d_worst);
+  if (n_services) *n_services = r->n_services;
+  return FM_OK;
+}
+
+int fm_result_timings(fm_result *r, float *ms, uint32_t cap) {
+  if (!r || !ms || cap < 4) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  FM_CUDA(ctx, cudaEventSynchronize(r->ev[4]));
+  for (int i = 0; i < 4; ++i) FM_CUDA(ctx, cudaEventElapsedTime(&ms[i], r->ev[i], r->ev[i + 1]));
+  return FM_OK;
+}
+
+void fm_result_free(fm_result *r) {
+  if (!r) return;
+  std::lock_guard<std::mutex> g(r->ctx->mu);
+  cudaSetDevice(r->ctx->device);
+  result_release(r);
+}
+
+// One-shot host-in / host-out scoring (the call a Go worker makes per sweep).
+int fm_score_host(fm_ctx *ctx, const fm_csr *host_csr, const fm_params *p, uint32_t n_services, fm_verdict *verdicts) {
+  if (!ctx || !host_csr || !p || !verdicts) return FM_E_INVALID;
+  fm_batch *b = nullptr;
+  int rc = fm_batch_from_csr(ctx, host_csr, &b);
+  if (rc) return rc;
+  if (n_services < b->n_services) { fm_batch_free(b); return set_err(ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1"); }
+  b->n_services = n_services;
+  fm_result *r = nullptr;
+  rc = fm_score(ctx, b, p, &r);
+  if (rc == FM_OK) {
+    uint64_t n = 0;
+    rc = fm_result_verdicts(r, verdicts, n_services, &n);
+    fm_result_free(r);
+  }
+  fm_batch_free(b);
+  return rc;
+}
+
+}  // extern "C"

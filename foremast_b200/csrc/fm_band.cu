@@ -1,0 +1,326 @@
+// fm_band.cu -- band models + anomaly flagging: moving-average band,
+// EWMA and double-exponential smoothing, fused with the flagging of the current window.
+//
+// Replaces the brain's "compute the historical model ... use threshold to detect current anomaly
+// data points" step (docs/guides/design.md:35, models list design.md:68-70, thresholds
+// deploy/foremast/3_brain/foremast-brain.yaml:26-73).
+//
+// Mapping: ONE THREAD PER SERIES-WINDOW, a warp owns 32 consecutive units.  The recurrences are
+// evaluated sequentially in sample order -- exactly the order of oracle/DECISIONS.md -- so sums,
+// bands and therefore flags are bit-identical to the CPU oracle; the parallelism comes from the
+// 10^5..10^7 independent series, not from scanning inside one.  HBM access stays coalesced by
+// staging: each warp pulls, per stage, a 128 B row (32 samples) of each of its 32 units with
+// 16 B cp.async copies (every 128 B line fully used by one instruction) into a 3-deep shared
+// memory ring, and each lane then walks its own row with conflict-free 128-bit LDS (row stride
+// 36 words).  Algorithmic bytes per unit: 4*(n_hist+n_base+n_cur) + 8 (offset) + 12 (lengths)
+// + results.
+#include "fm_common.cuh"
+
+namespace {
+
+constexpr int kChunk = 32;        // samples per row per stage
+constexpr int kRowWords = 36;     // 32 + 4 pad words: 16 B aligned rows, conflict-free LDS.128
+constexpr int kStages = 3;
+constexpr int kWarpsPerBlock = 4;
+constexpr int kRingBytes = kWarpsPerBlock * kStages * 32 * kRowWords * 4;
+constexpr int kSmemBytes = kRingBytes + kWarpsPerBlock * 32 * (8 + 4);
+
+struct Rule {
+  double k, mlb;
+  uint32_t bound;
+};
+
+template <uint32_t ALGS>
+struct State {
+  // MA_ALL
+  double x0, s1, s2, ma_up, ma_lo, ma_mean, ma_sd;
+  // EWMA
+  double es, esse, esig;
+  // DES
+  double dl, db, dsse, dsig;
+  uint32_t cnt[3], first[3];
+};
+
+__device__ __forceinline__ bool outside(double x, double up, double lo, uint32_t bound) {
+  return ((bound & 1u) && x > up) || ((bound & 2u) && x < lo);
+}
+
+template <uint32_t ALGS>
+__device__ __forceinline__ void src_update(State<ALGS> &s, double xd, double alpha, double ab) {
+  if (ALGS & FM_ALG_MA_ALL) {
+    double d = xd - s.x0;
+    s.s1 += d;
+    s.s2 = fma(d, d, s.s2);
+  }
+  if (ALGS & FM_ALG_EWMA) {
+    double e = xd - s.es;
+    s.esse = fma(e, e, s.esse);
+    s.es = fma(alpha, e, s.es);
+  }
+  if (ALGS & FM_ALG_DES) {
+    double f = s.dl + s.db, e = xd - f;
+    s.dsse = fma(e, e, s.dsse);
+    s.dl = fma(alpha, e, f);
+    s.db = fma(ab, e, s.db);
+  }
+}
+
+template <uint32_t ALGS>
+__device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t ns) {
+  if (ALGS & FM_ALG_MA_ALL) {
+    double m1 = s.s1 / (double)ns, mean = s.x0 + m1;
+    double var = fma(-m1, m1, s.s2 / (double)ns);
+    if (!(var > 0.0)) var = 0.0;
+    double sd = sqrt(var);
+    s.ma_mean = mean;
+    s.ma_sd = sd;
+    s.ma_up = fma(r.k, sd, mean);
+    double lo = fma(-r.k, sd, mean);
+    s.ma_lo = lo < r.mlb ? r.mlb : lo;
+  }
+  if (ALGS & FM_ALG_EWMA) s.esig = ns >= 2 ? sqrt(s.esse / (double)(ns - 1)) : 0.0;
+  if (ALGS & FM_ALG_DES) s.dsig = ns >= 2 ? sqrt(s.dsse / (double)(ns - 1)) : 0.0;
+}
+
+// One current point: flag against each band, then keep the smoothers running (D4).
+template <uint32_t ALGS>
+__device__ __forceinline__ void cur_update(State<ALGS> &s, const Rule &r, double xd, uint32_t j, bool valid,
+                                           double alpha, double ab, float &bup, float &blo, uint32_t band_alg) {
+  if (ALGS & FM_ALG_MA_ALL) {
+    bool f = valid && outside(xd, s.ma_up, s.ma_lo, r.bound);
+    if (f && s.cnt[0]++ == 0) s.first[0] = j;
+    if (band_alg == FM_ALG_MA_ALL) { bup = (float)s.ma_up; blo = (float)s.ma_lo; }
+  }
+  if (ALGS & FM_ALG_EWMA) {
+    double f0 = s.es, up = fma(r.k, s.esig, f0), lo = fma(-r.k, s.esig, f0);
+    lo = lo < r.mlb ? r.mlb : lo;
+    bool f = valid && outside(xd, up, lo, r.bound);
+    if (f && s.cnt[1]++ == 0) s.first[1] = j;
+    if (band_alg == FM_ALG_EWMA) { bup = (float)up; blo = (float)lo; }
+    double e = xd - f0;
+    s.es = fma(alpha, e, s.es);
+  }
+  if (ALGS & FM_ALG_DES) {
+    double f0 = s.dl + s.db, up = fma(r.k, s.dsig, f0), lo = fma(-r.k, s.dsig, f0);
+    lo = lo < r.mlb ? r.mlb : lo;
+    bool f = valid && outside(xd, up, lo, r.bound);
+    if (f && s.cnt[2]++ == 0) s.first[2] = j;
+    if (band_alg == FM_ALG_DES) { bup = (float)up; blo = (float)lo; }
+    double e = xd - f0;
+    s.dl = fma(alpha, e, f0);
+    s.db = fma(ab, e, s.db);
+  }
+}
+
+template <uint32_t ALGS, bool BANDS>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const DevParams *__restrict__ dp,
+                                                              bool rank_ran, fm_series_score *__restrict__ scores,
+                                                              uint32_t *__restrict__ unit_status,
+                                                              uint32_t *__restrict__ unit_points,
+                                                              float *__restrict__ band_up, float *__restrict__ band_lo) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
+  float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kStages * 32 * kRowWords);
+  int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingBytes) + warp * 32;
+  uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingBytes + kWarpsPerBlock * 32 * 8) + warp * 32;
+  const uint64_t u = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * 32 + lane;
+  const bool have = u < b.n_units;
+
+  // ---- per-lane unit description
+  int64_t off = 0;
+  uint32_t nh = 0, nb = 0, nc = 0, mt = 0, status = 0;
+  if (have) {
+    off = b.offsets[u];
+    nh = b.seg_lens[3 * u]; nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2];
+    mt = b.metric_type[u];
+    if (rank_ran) status = scores[u].status;
+  }
+  const uint32_t ntot = nh + nb + nc;
+  // model window (D15)
+  uint32_t a0 = 0, ns = 0;
+  const uint32_t min_hist = dp->min_historical;
+  if (nh >= min_hist && nh > 0) { a0 = 0; ns = nh; }
+  else if (nb >= min_hist && nb > 0) { a0 = nh; ns = nb; status |= FM_S_MODEL_BASE; }
+  const bool active = have && ns > 0 && nc > 0;
+  if (have && !active) status |= FM_S_UNKNOWN;
+  // ranges of this lane in unit coordinates; empty when inactive
+  const uint32_t a1 = active ? a0 + ns : 0, c0 = active ? nh + nb : 0, c1 = active ? ntot : 0;
+  if (!active) a0 = 0;
+
+  Rule r;
+  {
+    const DevRule &dr = dp->rules[mt < FM_MAX_METRIC_TYPES ? mt : 0];
+    r.k = (status & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
+    r.mlb = dr.min_lower_bound;
+    r.bound = dr.bound;
+  }
+  const double alpha = dp->alpha, ab = dp->alpha * dp->beta;
+  const uint32_t band_alg = BANDS ? dp->band_algorithm : 0u;
+
+  State<ALGS> s;
+  s.x0 = s.s1 = s.s2 = s.ma_up = s.ma_lo = s.ma_mean = s.ma_sd = 0.0;
+  s.es = s.esse = s.esig = 0.0;
+  s.dl = s.db = s.dsse = s.dsig = 0.0;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) { s.cnt[a] = 0; s.first[a] = FM_NONE_IDX; }
+
+  // ---- staging set-up
+  s_off[lane] = off;
+  s_len[lane] = active ? ((ntot + 3u) & ~3u) : 0u;   // inactive units are not even read
+  __syncwarp();
+  const uint32_t nchunks = (warp_max_u32(active ? ntot : 0u) + kChunk - 1) / kChunk;
+  const unsigned row_sub = lane >> 3, col4 = lane & 7;
+
+  auto issue = [&](uint32_t ch) {
+    if (ch < nchunks) {
+      float *dst = s_ring + (ch % kStages) * (32 * kRowWords);
+#pragma unroll
+      for (int rr = 0; rr < 8; ++rr) {
+        const unsigned row = rr * 4 + row_sub;
+        const uint32_t pos = ch * kChunk + col4 * 4;
+        if (pos < s_len[row])
+          cp_async16(dst + row * kRowWords + col4 * 4, b.values + s_off[row] + pos);
+      }
+    }
+    cp_async_commit();
+  };
+
+#pragma unroll
+  for (int st = 0; st < kStages - 1; ++st) issue(st);
+
+  for (uint32_t ch = 0; ch < nchunks; ++ch) {
+    cp_async_wait<kStages - 2>();
+    __syncwarp();
+    issue(ch + kStages - 1);
+
+    const float *row = s_ring + (ch % kStages) * (32 * kRowWords) + lane * kRowWords;
+    const uint32_t cs = ch * kChunk, ce = cs + kChunk;
+    const bool done = cs >= c1, not_started = ce <= a0;
+    const bool cls_src = cs >= a0 + 2 && ce <= a1;
+    const bool cls_cur = cs > c0 && ce <= c1;
+    const bool cls_skip = not_started || done || (cs >= a1 && ce <= c0);
+    const bool dontcare = !active || done || not_started;
+
+    if (__all_sync(0xffffffffu, cls_src || dontcare)) {
+      // whole chunk inside the model window for every lane: no range checks
+#pragma unroll
+      for (int v4 = 0; v4 < 8; ++v4) {
+        const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
+        src_update<ALGS>(s, (double)x.x, alpha, ab);
+        src_update<ALGS>(s, (double)x.y, alpha, ab);
+        src_update<ALGS>(s, (double)x.z, alpha, ab);
+        src_update<ALGS>(s, (double)x.w, alpha, ab);
+      }
+    } else if (!BANDS && __all_sync(0xffffffffu, cls_cur || dontcare)) {
+      float du, dl;
+#pragma unroll
+      for (int v4 = 0; v4 < 8; ++v4) {
+        const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
+        const uint32_t j = cs + v4 * 4 - c0;
+        cur_update<ALGS>(s, r, (double)x.x, j + 0, cls_cur, alpha, ab, du, dl, 0u);
+        cur_update<ALGS>(s, r, (double)x.y, j + 1, cls_cur, alpha, ab, du, dl, 0u);
+        cur_update<ALGS>(s, r, (double)x.z, j + 2, cls_cur, alpha, ab, du, dl, 0u);
+        cur_update<ALGS>(s, r, (double)x.w, j + 3, cls_cur, alpha, ab, du, dl, 0u);
+      }
+    } else if (!__all_sync(0xffffffffu, cls_skip)) {
+      // generic path: chunk straddles a segment edge for at least one lane
+      if (active && !done && !not_started) {
+        for (int i = 0; i < kChunk; ++i) {
+          const uint32_t t = cs + i;
+          const double xd = (double)row[i];
+          if (t >= a0 && t < a1) {
+            if (t == a0) {
+              s.x0 = xd; s.s1 = 0.0; s.s2 = 0.0;
+              s.es = xd; s.esse = 0.0;
+              s.dl = xd; s.db = 0.0; s.dsse = 0.0;
+            } else {
+              if (t == a0 + 1) s.db = xd - s.dl;
+              src_update<ALGS>(s, xd, alpha, ab);
+            }
+          } else if (t >= c0 && t < c1) {
+            if (t == c0) finalize<ALGS>(s, r, ns);
+            float bu = 0.f, bl = 0.f;
+            cur_update<ALGS>(s, r, xd, t - c0, true, alpha, ab, bu, bl, band_alg);
+            if (BANDS && band_alg) { band_up[off + t] = bu; band_lo[off + t] = bl; }
+          }
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+
+  // ---- results
+  if (have) {
+    fm_series_score *o = scores + u;
+    uint32_t pts = 0;
+    if (active) {
+      const uint32_t min_pts = dp->min_anomaly_points;
+      if (ALGS & FM_ALG_MA_ALL) {
+        status |= 1u << (FM_S_ALG_SHIFT + 0);
+        o->n_anom[0] = s.cnt[0]; o->first_idx[0] = s.first[0];
+        o->ma_mean = s.ma_mean; o->ma_std = s.ma_sd; o->sigma[0] = s.ma_sd;
+        if (s.cnt[0] > 0 && s.cnt[0] >= min_pts) status |= FM_S_ANOMALY;
+        pts = max(pts, s.cnt[0]);
+      }
+      if (ALGS & FM_ALG_EWMA) {
+        status |= 1u << (FM_S_ALG_SHIFT + 2);
+        o->n_anom[2] = s.cnt[1]; o->first_idx[2] = s.first[1]; o->sigma[2] = s.esig;
+        if (s.cnt[1] > 0 && s.cnt[1] >= min_pts) status |= FM_S_ANOMALY;
+        pts = max(pts, s.cnt[1]);
+      }
+      if ((ALGS & FM_ALG_DES) && ns >= 2) {
+        status |= 1u << (FM_S_ALG_SHIFT + 3);
+        o->n_anom[3] = s.cnt[2]; o->first_idx[3] = s.first[2]; o->sigma[3] = s.dsig;
+        if (s.cnt[2] > 0 && s.cnt[2] >= min_pts) status |= FM_S_ANOMALY;
+        pts = max(pts, s.cnt[2]);
+      }
+    }
+    o->status = status;
+    o->k_eff = r.k;
+    if (!rank_ran) { o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0; }
+    unit_status[u] = status;
+    unit_points[u] = pts;
+  }
+}
+
+template <uint32_t ALGS>
+cudaError_t launch(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_series_score *scores,
+                   uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo, cudaStream_t st) {
+  const uint64_t per_block = kWarpsPerBlock * 32;
+  const unsigned grid = (unsigned)((b.n_units + per_block - 1) / per_block);
+  if (grid == 0) return cudaSuccess;
+  cudaError_t e;
+  if (band_up && band_lo) {
+    e = cudaFuncSetAttribute(k_band<ALGS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (e != cudaSuccess) return e;
+    k_band<ALGS, true><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo);
+  } else {
+    e = cudaFuncSetAttribute(k_band<ALGS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (e != cudaSuccess) return e;
+    k_band<ALGS, false><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points, nullptr, nullptr);
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+// algorithms: subset of {MA_ALL, EWMA, DES}; 0 still runs (it resolves unknown units and statuses).
+cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
+                           fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
+                           float *band_up, float *band_lo, cudaStream_t st) {
+  const uint32_t a = algorithms & (FM_ALG_MA_ALL | FM_ALG_EWMA | FM_ALG_DES);
+#define FM_BAND_CASE(M) \
+  case M: return launch<M>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo, st);
+  switch (a) {
+    FM_BAND_CASE(0u)
+    FM_BAND_CASE(FM_ALG_MA_ALL)
+    FM_BAND_CASE(FM_ALG_EWMA)
+    FM_BAND_CASE(FM_ALG_DES)
+    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_EWMA)
+    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_DES)
+    FM_BAND_CASE(FM_ALG_EWMA | FM_ALG_DES)
+    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_EWMA | FM_ALG_DES)
+  }
+#undef FM_BAND_CASE
+  return cudaErrorInvalidValue;
+}

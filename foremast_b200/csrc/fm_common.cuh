@@ -1,0 +1,75 @@
+// fm_common.cuh -- shared device-side definitions for libforemast_gpu (sm_100a only).
+//
+// Numerics contract (oracle/DECISIONS.md "Exact arithmetic"): the library is compiled with
+// --fmad=false, every fused multiply-add below is an explicit fma(); that is what makes integer
+// statistics and verdicts reproducible bit for bit against the CPU oracle.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/foremast_gpu.h"
+
+#define FM_WARP 32
+#define FM_NONE_IDX 0xFFFFFFFFu
+
+// Device view of a sealed batch: ragged CSR in HBM.
+struct DevBatch {
+  uint64_t n_units;
+  const float *values;        // fp32 samples, unit starts 16 B aligned
+  const int64_t *offsets;     // [n_units+1]
+  const uint32_t *seg_lens;   // [3*n_units] hist, base, cur
+  const uint32_t *service_id; // [n_units]
+  const uint8_t *metric_type; // [n_units]
+  uint64_t first_unit;        // global index of unit 0 (multi-GPU shards)
+};
+
+struct DevRule {
+  double threshold, min_lower_bound;
+  uint32_t bound, pad;
+};
+
+// fm_params resolved for the device (rows with bound == 0 already replaced by row 0, D16).
+struct DevParams {
+  uint32_t algorithms, pairwise;
+  double pairwise_threshold, differ_scale;
+  uint32_t min_mann_white, min_wilcoxon, min_kruskal, min_historical;
+  uint32_t min_anomaly_points, ma_window, period, band_algorithm;
+  double alpha, beta, gamma;
+  DevRule rules[FM_MAX_METRIC_TYPES];
+};
+
+__device__ __forceinline__ unsigned fm_lane() { return threadIdx.x & 31u; }
+
+__device__ __forceinline__ int64_t warp_sum_i64(int64_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+
+// 16-byte async global->shared copy (LDGSTS); the staging primitive of the band kernel.
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// kernels (one translation unit each)
+void fm_launch_synth(const fm_synth_config &cfg, uint64_t stride, float *values, int64_t *offsets,
+                     uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type, cudaStream_t st);
+void fm_launch_batch_stats(const DevBatch &b, uint32_t *out6, cudaStream_t st);
+cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t max_seg, fm_series_score *scores,
+                           int sm_count, cudaStream_t st);
+cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
+                           fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
+                           float *band_up, float *band_lo, cudaStream_t st);
+void fm_launch_verdict_reduce(const DevBatch &b, const uint32_t *unit_status, const uint32_t *unit_points,
+                              uint32_t n_services, uint32_t *counts, unsigned long long *worst, cudaStream_t st);
+void fm_launch_verdict_finalize(uint32_t n_services, const uint32_t *counts, const unsigned long long *worst,
+                                fm_verdict *out, cudaStream_t st);

@@ -206,6 +206,10 @@ const char *fm_last_error(const fm_ctx *ctx);
 void fm_params_default(fm_params *p);
 int fm_device_info(const fm_ctx *ctx, int32_t *sm_count, uint64_t *hbm_bytes, char *name, uint32_t name_cap);
 
+/* CUDA-event stopwatch on the context's stream (all library work is ordered on it). */
+int fm_timer_start(fm_ctx *ctx);
+int fm_timer_stop(fm_ctx *ctx, float *ms);
+
 /* Pinned host memory for callers that want zero-copy staging of large CSR batches. */
 int fm_host_alloc(fm_ctx *ctx, uint64_t bytes, void **out);
 void fm_host_free(fm_ctx *ctx, void *p);
@@ -229,6 +233,10 @@ int fm_batch_from_csr(fm_ctx *ctx, const fm_csr *host_csr, fm_batch **out);
 int fm_batch_from_device(fm_ctx *ctx, const fm_csr *device_csr, fm_batch **out);
 /* Generate the synthetic workload of SURVEY 8(d) directly in HBM. */
 int fm_batch_synth(fm_ctx *ctx, const fm_synth_config *cfg, fm_batch **out);
+/* Multi-GPU shards: global index of this batch's unit 0 and the global service count, so that
+ * every shard fills the same dense per-service vector (the reference scales the same way, with
+ * shared-nothing brain pods, docs/guides/design.md:37-41). */
+int fm_batch_set_shard(fm_batch *b, uint64_t first_unit, uint32_t n_services);
 int fm_batch_info(const fm_batch *b, uint64_t *n_units, uint64_t *n_values, uint32_t *n_services);
 /* Copy the packed CSR back to host buffers (tests, CPU baseline); any pointer may be NULL. */
 int fm_batch_download(const fm_batch *b, float *values, int64_t *offsets, uint32_t *seg_lens,
@@ -256,7 +264,8 @@ int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uin
  * counts = uint32[4*n_services] (n_units, n_unknown, n_anom_units, n_anom_points), summed;
  * worst  = uint64[n_services]   ((points << 32) | ~unit), maxed. */
 int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst, uint32_t *n_services);
-/* Kernel time of the last fm_score in milliseconds, per stage (rank, band, verdict), CUDA events. */
+/* Device time of this fm_score in milliseconds per stage: {set-up (allocation, clears), rank kernel,
+ * band kernel, verdict reduce}; CUDA events on the context's stream; cap >= 4. */
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap);
 void fm_result_free(fm_result *r);
 

@@ -1,0 +1,274 @@
+"""GPU parity tests: the CUDA path through the C ABI versus the CPU oracle on the same inputs.
+
+Bar (BASELINE.json north_star): rank statistics, anomaly counts/indices, statuses and verdicts
+bit-identical; smoothed values, sigmas, bands, H and p-values within 1e-5 relative."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from foremast_b200 import _abi as abi
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5  # north_star tolerance for floating-point outputs
+INT_FIELDS = ["status", "n_anom", "first_idx", "w_n", "mw_2u1", "mw_2r1", "mw_ties", "w_2wplus", "w_2wminus", "w_ties"]
+FLT_FIELDS = ["p_mw", "p_w", "p_k", "kw_h", "k_eff", "ma_mean", "ma_std", "sigma"]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from foremast_b200.api import Context
+    c = Context()
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import oracle as o
+    return o
+
+
+def assert_scores_equal(got, ref):
+    for f in INT_FIELDS:
+        assert np.array_equal(got[f], ref[f]), (f, np.argwhere(got[f] != ref[f])[:5], got[f][got[f] != ref[f]][:5], ref[f][got[f] != ref[f]][:5])
+    worst = 0.0
+    for f in FLT_FIELDS:
+        a, b = got[f].astype(np.float64), ref[f].astype(np.float64)
+        err = np.abs(a - b) / np.maximum(np.abs(b), 1e-300)
+        err[(a == b)] = 0.0
+        assert np.all(err <= REL_TOL), (f, float(err.max()))
+        worst = max(worst, float(err.max()) if err.size else 0.0)
+    return worst
+
+
+def full_params(oracle, algs=abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES, pairwise=abi.PW_ALL):
+    p = oracle.params_default()
+    p.algorithms = algs
+    p.pairwise = pairwise
+    return p
+
+
+def check_batch(ctx, oracle, batch, p, n_services=None):
+    host = batch.download()
+    res = ctx.score(batch, p)
+    got = res.series()
+    ref, _, _ = oracle.score(host, p)
+    worst = assert_scores_equal(got, ref)
+    ns = batch.info()["n_services"]
+    v_ref = oracle.verdicts(host, ref, ns)
+    v_got = res.verdicts()
+    assert v_got.tobytes() == v_ref.tobytes()
+    res.free()
+    return got, worst
+
+
+def test_synth_generator_bit_identical(ctx, oracle):
+    for shape in [(0, 60, 30), (100, 30, 30), (1440, 0, 60), (33, 7, 1)]:
+        flags = abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES
+        b = ctx.batch_synth(517, *shape, units_per_service=40, n_metric_types=8, flags=flags, first_unit=1000)
+        g = b.download()
+        h = oracle.synth(517, *shape, units_per_service=40, n_metric_types=8, flags=flags, first_unit=1000)
+        assert np.array_equal(g.offsets, h.offsets) and np.array_equal(g.seg_lens, h.seg_lens)
+        assert np.array_equal(g.service_id, h.service_id) and np.array_equal(g.metric_type, h.metric_type)
+        assert g.values.view(np.uint32).tobytes() == h.values.view(np.uint32).tobytes()
+        b.free()
+
+
+def test_demo_fixture_through_incremental_ingest(ctx, oracle, golden_dir):
+    """The reference's demo profile data1.txt / data2.txt (spikes at idx 1 and 21) -> unhealthy."""
+    fx = json.load(open(os.path.join(golden_dir, "demo_fixture.json")))
+    p = oracle.params_default()
+    b = ctx.batch_from_units([([], fx["data1"], fx["data2"])], metric_type=[abi.MT_ERROR5XX])
+    res = ctx.score(b, p)
+    s = res.series()[0]
+    g = fx["pooled"]
+    assert (int(s["mw_2r1"]), int(s["mw_2u1"]), int(s["mw_ties"])) == (g["mw_2r1"], g["mw_2u1"], g["mw_ties"]) == (2946, 1614, 76068)
+    assert (int(s["w_n"]), int(s["w_2wplus"]), int(s["w_2wminus"]), int(s["w_ties"])) == (g["w_n"], g["w_2wplus"], g["w_2wminus"], g["w_ties"])
+    for k in ("p_mw", "p_k", "p_w", "kw_h"):
+        assert abs(s[k] - g[k]) / g[k] < REL_TOL
+    assert int(s["n_anom"][0]) == 2 and int(s["first_idx"][0]) == 1
+    v = res.verdicts()
+    assert int(v[0]["verdict"]) == abi.V_UNHEALTH and abi.V_STATUS[int(v[0]["verdict"])] == "completed_unhealth"
+    res.free()
+    b.free()
+
+
+def test_rank_cases_fixture(ctx, oracle, golden_dir):
+    cases = json.load(open(os.path.join(golden_dir, "rank_cases.json")))["cases"]
+    p = oracle.params_default()
+    p.min_mann_white = p.min_wilcoxon = p.min_kruskal = 1
+    b = ctx.batch_from_units([([], c["x"], c["y"]) for c in cases])
+    res = ctx.score(b, p)
+    sc = res.series()
+    for c, s in zip(cases, sc):
+        if c.get("degenerate"):
+            assert s["p_mw"] == 1.0 and s["p_k"] == 1.0 and s["p_w"] == 1.0
+            continue
+        for k in ("mw_2r1", "mw_2u1", "mw_ties", "w_n"):
+            assert int(s[k]) == c[k], k
+        if c["w_n"]:
+            for k in ("w_2wplus", "w_2wminus", "w_ties"):
+                assert int(s[k]) == c[k], k
+        assert abs(s["p_mw"] - c["p_mw"]) <= REL_TOL * c["p_mw"]
+        assert abs(s["p_k"] - c["p_k"]) <= REL_TOL * c["p_k"]
+    res.free()
+    b.free()
+
+
+@pytest.mark.parametrize("shape,n", [((0, 60, 30), 5), ((0, 720, 720), 3000), ((1440, 0, 60), 2000),
+                                      ((300, 100, 90), 4097), ((10080, 30, 30), 300), ((0, 1024, 1024), 257)])
+def test_score_parity_on_synthetic_batches(ctx, oracle, shape, n):
+    flags = abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES
+    b = ctx.batch_synth(n, *shape, units_per_service=80 if n > 100 else 5, n_metric_types=8 if n > 5 else 5, flags=flags)
+    p = full_params(oracle)
+    got, worst = check_batch(ctx, oracle, b, p)
+    if n > 1000:
+        assert (got["status"] & abi.S_ANOMALY).any() and (got["status"] & abi.S_UNKNOWN).any()
+    print(f"shape={shape} n={n} worst float rel err {worst:.3e}")
+    b.free()
+
+
+@pytest.mark.parametrize("pairwise", [abi.PW_NONE, abi.PW_ANY, abi.PW_MANN_WHITE, abi.PW_WILCOXON, abi.PW_KRUSKAL])
+@pytest.mark.parametrize("algs", [abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES, abi.ALG_MA_ALL | abi.ALG_DES])
+def test_parameter_combinations(ctx, oracle, pairwise, algs):
+    b = ctx.batch_synth(1500, 200, 64, 64, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=7 + pairwise)
+    p = full_params(oracle, algs, pairwise)
+    check_batch(ctx, oracle, b, p)
+    b.free()
+
+
+def test_edge_cases(ctx, oracle):
+    rng = np.random.default_rng(11)
+    z = rng.normal(10, 1, 200).astype(np.float32)
+    units = [
+        ([], [], []),                       # empty unit
+        (z[:50], [], []),                   # no current -> unknown
+        ([], z[:4], z[4:40]),               # model window too short -> unknown, tests gated off
+        (z[:50], z[50:55], z[60:90]),       # baseline below MIN_* -> no rank tests
+        ([1.5] * 40, [1.5] * 30, [1.5] * 30),   # constant series, all ties
+        ([0.0] * 40, [0.0] * 30, [0.0] * 29 + [5.0]),  # zeros then a spike
+        (z[:10], z[10:30], z[30:50]),       # exactly at the minimum sizes
+        (z[:1], z[:33], z[33:66]),          # hist too short, base is the model window
+        ([], z[:100], z[100:101]),          # single current point
+        ([-0.0, 0.0, 1.0] * 10, [-0.0] * 20, [0.0] * 20),  # signed zeros (canonicalised at ingest)
+        ([float("nan"), 1.0, float("inf")] + list(z[:30]), z[30:60], z[60:90]),  # gaps dropped at ingest
+    ]
+    sid = [0, 0, 1, 1, 2, 2, 3, 3, 4, 5, 5]
+    mt = [abi.MT_CPU, abi.MT_LATENCY, abi.MT_ERROR5XX, abi.MT_MEMORY, abi.MT_ERROR4XX, abi.MT_ERROR5XX,
+          abi.MT_TPS, 15, 200, abi.MT_LATENCY, abi.MT_CPU]
+    b = ctx.batch_from_units(units, service_id=sid, metric_type=mt)
+    host = b.download()
+    assert list(host.seg_lens[10]) == [31, 30, 30]
+    p = full_params(oracle)
+    got, _ = check_batch(ctx, oracle, b, p)
+    assert got[0]["status"] & abi.S_UNKNOWN and got[1]["status"] & abi.S_UNKNOWN and got[2]["status"] & abi.S_UNKNOWN
+    assert got[5]["status"] & abi.S_ANOMALY and not got[4]["status"] & abi.S_ANOMALY
+    b.free()
+    # empty batch
+    e = ctx.batch_from_units([])
+    r = ctx.score(e, p)
+    assert r.series().size == 0 and r.verdicts().size == 0
+    r.free()
+    e.free()
+
+
+def test_bulk_csr_ingest_and_realignment(ctx, oracle):
+    h = oracle.synth(300, 50, 21, 22, flags=abi.SYNTH_ANOMALIES)
+    p = full_params(oracle)
+    b = ctx.batch_from_csr(h)
+    check_batch(ctx, oracle, b, p)
+    b.free()
+    # unaligned CSR (units packed back to back) is re-packed by the library
+    vals, offs, pos = [], [], 0
+    for u in range(h.n_units):
+        hs, bs, cs = h.segments(u)
+        offs.append(pos)
+        vals += [hs, bs, cs]
+        pos += hs.size + bs.size + cs.size
+    offs.append(pos)
+    packed = abi.HostCsr(np.concatenate(vals), offs, h.seg_lens, h.service_id, h.metric_type)
+    b2 = ctx.batch_from_csr(packed)
+    ref, _, _ = oracle.score(h, p)
+    r2 = ctx.score(b2, p)
+    assert_scores_equal(r2.series(), ref)
+    v = ctx.score_host(packed, p)
+    assert v.tobytes() == oracle.verdicts(h, ref, h.n_services).tobytes()
+    r2.free()
+    b2.free()
+
+
+def test_bands_materialised(ctx, oracle):
+    b = ctx.batch_synth(200, 300, 0, 45, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+    host = b.download()
+    for alg in (abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES):
+        p = full_params(oracle, abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES, abi.PW_NONE)
+        p.band_algorithm = alg
+        ref, up, lo = oracle.score(host, p, want_bands=True)
+        res = ctx.score(b, p)
+        assert_scores_equal(res.series(), ref)
+        for u in (0, 7, 50, 199):
+            gu, gl = res.bands(u)
+            o = int(host.offsets[u]) + int(host.seg_lens[u][0]) + int(host.seg_lens[u][1])
+            n = int(host.seg_lens[u][2])
+            assert gu.size == n
+            assert np.array_equal(gu, up[o:o + n]) and np.array_equal(gl, lo[o:o + n])
+        res.free()
+    b.free()
+
+
+def test_device_csr_and_alignment_errors(ctx, oracle):
+    import torch
+    from foremast_b200._lib import ForemastGpuError
+    h = oracle.synth(64, 40, 20, 20)
+    dv = torch.from_numpy(h.values).cuda()
+    do = torch.from_numpy(h.offsets).cuda()
+    ds = torch.from_numpy(h.seg_lens.astype(np.int32)).cuda()
+    di = torch.from_numpy(h.service_id.astype(np.int32)).cuda()
+    dm = torch.from_numpy(h.metric_type).cuda()
+    b = ctx.batch_from_device(64, dv.data_ptr(), do.data_ptr(), ds.data_ptr(), di.data_ptr(), dm.data_ptr(), keepalive=(dv, do, ds, di, dm))
+    check_batch(ctx, oracle, b, full_params(oracle))
+    b.free()
+    bad = do.clone()
+    bad[3] += 1
+    with pytest.raises(ForemastGpuError) as ei:
+        ctx.batch_from_device(64, dv.data_ptr(), bad.data_ptr(), ds.data_ptr(), di.data_ptr(), dm.data_ptr())
+    assert ei.value.code == abi.E_ALIGN
+
+
+def test_full_size_properties(ctx, oracle):
+    """BASELINE.json headline shape: 1M series-windows x 1440 points (720 baseline + 720 current),
+    all scorers.  Size-independent properties on everything, bit-exact oracle check on a sample."""
+    n = 1_000_000
+    b = ctx.batch_synth(n, 0, 720, 720, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+    p = full_params(oracle)
+    res = ctx.score(b, p)
+    sc = res.series()
+    st = sc["status"]
+    ran = (st & abi.S_MW_RUN) != 0
+    assert ran.mean() > 0.99
+    assert np.all(sc["mw_2u1"][ran] >= 0) and np.all(sc["mw_2u1"][ran] <= 2 * 720 * 720)
+    wn = sc["w_n"].astype(np.int64)
+    assert np.array_equal(sc["w_2wplus"] + sc["w_2wminus"], wn * (wn + 1))
+    assert np.all((sc["p_mw"] >= 0) & (sc["p_mw"] <= 1) & (sc["p_k"] >= 0) & (sc["p_k"] <= 1))
+    v = res.verdicts()
+    assert int(v["n_units"].sum()) == n
+    assert int(v["n_anom_units"].sum()) == int(((st & abi.S_ANOMALY) != 0).sum())
+    assert int(v["n_unknown"].sum()) == int(((st & abi.S_UNKNOWN) != 0).sum())
+    assert np.array_equal(v["verdict"] == abi.V_UNHEALTH, v["n_anom_units"] > 0)
+    # idempotence: scoring the same batch again gives the same bytes
+    res2 = ctx.score(b, p)
+    assert res2.series().tobytes() == sc.tobytes()
+    res2.free()
+    # bit-exact against the oracle on a strided sample of units
+    host = b.download()
+    idx = np.arange(0, n, 997)[:1000]
+    stride = int(host.offsets[1])
+    sub = abi.HostCsr(np.concatenate([host.values[i * stride:(i + 1) * stride] for i in idx] + [np.zeros(32, np.float32)]),
+                      np.arange(len(idx) + 1) * stride, host.seg_lens[idx], host.service_id[idx], host.metric_type[idx])
+    ref, _, _ = oracle.score(sub, p)
+    assert_scores_equal(sc[idx], ref)
+    res.free()
+    b.free()

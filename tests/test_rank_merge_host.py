@@ -1,0 +1,71 @@
+"""The per-lane merge-path / tie-group bookkeeping of the rank kernel
+(foremast_b200/csrc/fm_rank_merge.h) is plain C++; compile it for the host and check it against
+a brute-force rank computation, including the heavy-tie and disjoint-range shapes that stress the
+galloping and the span hand-over between lanes."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+from scipy import stats
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def harness(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("rm") / "rank_merge_host")
+    subprocess.run(["/usr/bin/g++", "-O1", "-std=c++17", "-o", exe,
+                    os.path.join(ROOT, "tests", "host", "rank_merge_host.cpp")], check=True)
+    return exe
+
+
+def brute(x, y):
+    pooled = np.concatenate([x, y]).astype(np.float64)
+    r = stats.rankdata(pooled)
+    _, cnt = np.unique(pooled, return_counts=True)
+    return int(round(2 * r[:len(x)].sum())), int((cnt.astype(np.int64) ** 3 - cnt).sum())
+
+
+def test_merge_walk_matches_bruteforce(harness):
+    rng = np.random.default_rng(3)
+    cases, expect = [], []
+    shapes = [(1, 1), (5, 3), (31, 33), (64, 64), (720, 720), (1000, 17), (17, 1000), (1024, 1024)]
+    for na, nb in shapes:
+        for kind in range(6):
+            if kind == 0:
+                x, y = rng.normal(0, 1, na), rng.normal(0, 1, nb)
+            elif kind == 1:   # heavy ties
+                x, y = rng.integers(0, 3, na), rng.integers(0, 3, nb)
+            elif kind == 2:   # all equal
+                x, y = np.ones(na), np.ones(nb)
+            elif kind == 3:   # disjoint, current above baseline
+                x, y = rng.normal(0, 1, na), rng.normal(100, 1, nb)
+            elif kind == 4:   # current entirely inside one gap of the baseline
+                x = np.concatenate([rng.normal(-50, 1, na // 2), rng.normal(50, 1, na - na // 2)])
+                y = rng.integers(0, 2, nb) * 0.5
+            else:             # moderate ties
+                x, y = np.round(rng.normal(0, 2, na)), np.round(rng.normal(0.5, 2, nb))
+            x = np.sort(x.astype(np.float32))
+            y = np.sort(y.astype(np.float32))
+            cases.append("m %d %d %s %s" % (na, nb, " ".join(repr(float(v)) for v in x),
+                                            " ".join(repr(float(v)) for v in y)))
+            expect.append(brute(x, y))
+    # Wilcoxon keys
+    for n in (1, 7, 32, 33, 720, 1024):
+        for kind in range(3):
+            d = (rng.normal(0, 1, n) if kind == 0 else rng.integers(-3, 4, n) if kind == 1
+                 else rng.choice([-1.0, 1.0], n)).astype(np.float32)
+            d = d[d != 0]
+            if d.size == 0:
+                d = np.array([1.0], np.float32)
+            keys = (np.abs(d).view(np.uint32).astype(np.uint64) << 1) | (d < 0)
+            keys = np.sort(keys)
+            cases.append("w %d %s" % (keys.size, " ".join(str(int(k)) for k in keys)))
+            r = stats.rankdata(np.abs(d).astype(np.float64))
+            _, cnt = np.unique(np.abs(d), return_counts=True)
+            expect.append((int(round(2 * r[d > 0].sum())), int((cnt.astype(np.int64) ** 3 - cnt).sum())))
+    inp = "%d\n%s\n" % (len(cases), "\n".join(cases))
+    out = subprocess.run([harness], input=inp, capture_output=True, text=True, check=True).stdout.split("\n")
+    got = [tuple(int(v) for v in line.split()) for line in out if line.strip()]
+    assert got == expect
