@@ -1,6 +1,7 @@
 """Object layer over the C ABI: Context / Batch / Result.  Mirrors the order of the brain's
 pass (ingest -> pairwise -> model -> flags -> verdict, docs/guides/design.md:35) and nothing else."""
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -21,6 +22,7 @@ class Context:
         rc = self._L.fm_init(C.byref(abi.Config(device, 0)), C.byref(self._h))
         if rc:
             raise ForemastGpuError(rc, self._L.fm_strerror(rc).decode())
+        self._children = weakref.WeakSet()  # batches/results must not outlive the context
 
     def _check(self, rc):
         if rc:
@@ -29,8 +31,16 @@ class Context:
 
     def close(self):
         if self._h:
+            for child in sorted(self._children, key=lambda c: isinstance(c, Batch)):
+                child.free()  # results first, then batches
             self._L.fm_shutdown(self._h)
             self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def __enter__(self):
         return self
@@ -118,6 +128,7 @@ class Context:
 class Batch:
     def __init__(self, ctx, handle):
         self.ctx, self._h, self._keepalive = ctx, handle, None
+        ctx._children.add(self)
 
     def info(self):
         n, nv, ns = C.c_uint64(), C.c_uint64(), C.c_uint32()
@@ -141,9 +152,9 @@ class Batch:
         return abi.HostCsr(values, offsets, seg, sid, mt)
 
     def free(self):
-        if self._h:
+        if self._h and self.ctx._h:
             self.ctx._L.fm_batch_free(self._h)
-            self._h = C.c_void_p()
+        self._h = C.c_void_p()
 
     def __del__(self):
         try:
@@ -155,6 +166,7 @@ class Batch:
 class Result:
     def __init__(self, ctx, batch, handle):
         self.ctx, self.batch, self._h = ctx, batch, handle
+        ctx._children.add(self)
 
     def sync(self):
         self.ctx._check(self.ctx._L.fm_result_sync(self._h))
@@ -191,9 +203,9 @@ class Result:
         return {"setup": ms[0], "rank": ms[1], "band": ms[2], "verdict": ms[3]}
 
     def free(self):
-        if self._h:
+        if self._h and self.ctx._h:
             self.ctx._L.fm_result_free(self._h)
-            self._h = C.c_void_p()
+        self._h = C.c_void_p()
 
     def __del__(self):
         try:

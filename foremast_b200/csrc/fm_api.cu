@@ -453,7 +453,10 @@ int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaMemcpyAsync(h_stats, d_stats, sizeof(h_stats), cudaMemcpyDeviceToHost, ctx->stream);
+  int64_t end_off = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&end_off, d->offsets + d->n_units, sizeof(end_off), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  b->n_values = (uint64_t)(end_off > 0 ? end_off : 0) + 32;  // the ABI requires 32 readable elements of slack
   if (d_stats) cudaFreeAsync(d_stats, ctx->stream);
   if (e != cudaSuccess) {
     delete b;

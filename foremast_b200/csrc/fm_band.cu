@@ -253,6 +253,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   if (have) {
     fm_series_score *o = scores + u;
     uint32_t pts = 0;
+#pragma unroll
+    for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
     if (active) {
       const uint32_t min_pts = dp->min_anomaly_points;
       if (ALGS & FM_ALG_MA_ALL) {

@@ -126,7 +126,7 @@ def test_score_parity_on_synthetic_batches(ctx, oracle, shape, n):
     p = full_params(oracle)
     got, worst = check_batch(ctx, oracle, b, p)
     if n > 1000:
-        assert (got["status"] & abi.S_ANOMALY).any() and (got["status"] & abi.S_UNKNOWN).any()
+        assert (got["status"] & abi.S_ANOMALY).any() and not (got["status"] & abi.S_ANOMALY).all()
     print(f"shape={shape} n={n} worst float rel err {worst:.3e}")
     b.free()
 
