@@ -8,7 +8,7 @@ import os
 from . import _abi as abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libforemast_gpu.so")
+LIB_PATH = os.environ.get("FOREMAST_GPU_LIB", os.path.join(_HERE, "libforemast_gpu.so"))
 
 # every symbol include/foremast_gpu.h declares: (name, restype, argtypes)
 _P = C.c_void_p

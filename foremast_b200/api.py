@@ -67,7 +67,6 @@ class Context:
         self._check(self._L.fm_host_alloc(self._h, nbytes, C.byref(p)))
         buf = (C.c_uint8 * nbytes).from_address(p.value)
         arr = np.frombuffer(buf, dtype=np.uint8)
-        arr._fm_ptr = None
         return arr, p.value
 
     def host_free(self, ptr):

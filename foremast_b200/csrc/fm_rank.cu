@@ -16,8 +16,6 @@
 // sums and tie terms.  Reads are plain coalesced 4-byte loads: segment starts are not 16 B
 // aligned in general, and this kernel is issue-bound on the sort, not on HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
-#include <math_constants.h>
-
 #include "fm_common.cuh"
 #include "fm_rank_merge.h"
 
@@ -26,63 +24,79 @@ namespace {
 constexpr int kWarpsPerBlock = 4;
 constexpr uint32_t kKeySentinel = 0xFFFFFFFFu;
 
-__device__ __forceinline__ float sel_minmax(bool lower, float a, float b) { return lower ? fminf(a, b) : fmaxf(a, b); }
 __device__ __forceinline__ uint32_t sel_minmax(bool lower, uint32_t a, uint32_t b) { return lower ? min(a, b) : max(a, b); }
-__device__ __forceinline__ void cex(float &a, float &b) { float lo = fminf(a, b), hi = fmaxf(a, b); a = lo; b = hi; }
 __device__ __forceinline__ void cex(uint32_t &a, uint32_t &b) { uint32_t lo = min(a, b), hi = max(a, b); a = lo; b = hi; }
 
-// Ascending bitonic sort of 32*R keys held as v[r] = element lane*R + r.  Every merge starts
+// order-preserving map of a finite float onto uint32 (x + 0.0f folds -0.0 into +0.0)
+__device__ __forceinline__ uint32_t float_key(float x) {
+  const uint32_t u = __float_as_uint(x + 0.0f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// Ascending bitonic sort of 32*R u32 keys held as v[r] = element lane*R + r.  Every merge starts
 // with a "mirror" step (partner = e ^ (k-1)) so all compare-exchanges point the same way and no
-// direction flags are needed; steps whose stride stays below R are pure register work.
-template <int R, typename T>
-__device__ __forceinline__ void warp_bitonic_sort(T (&v)[R], const unsigned lane) {
+// direction flags are needed.  Phase 1 sorts the R keys of each lane in registers; phase 2 runs
+// the five cross-lane merges as a ROLLED loop (lane masks are runtime values, register indices
+// stay static) so the whole sort is ~1k instructions and stays in the instruction cache -- the
+// fully unrolled network (12k instructions per kernel) stalled 7 of 8 issue slots on fetch.
+template <int R>
+__device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsigned lane) {
 #pragma unroll
-  for (int k = 2; k <= 32 * R; k <<= 1) {
-    if (k <= R) {
+  for (int k = 2; k <= R; k <<= 1) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int pr = r ^ (k - 1);
+      if (pr > r) cex(v[r], v[pr]);
+    }
+#pragma unroll
+    for (int j = k >> 2; j >= 1; j >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const int pr = r ^ (k - 1);
+        const int pr = r ^ j;
         if (pr > r) cex(v[r], v[pr]);
       }
-    } else {
-      const unsigned lm = k / R - 1;
-      const bool lower = (lane & (k / R / 2)) == 0;
+    }
+  }
+#pragma unroll 1
+  for (unsigned kk = 1; kk <= 16; kk <<= 1) {  // merge size k = 2*R*kk
+    {
+      const unsigned lm = 2 * kk - 1;
+      const bool lower = (lane & kk) == 0;
       if (R == 1) {
-        T a = __shfl_xor_sync(0xffffffffu, v[0], lm);
+        const uint32_t a = __shfl_xor_sync(0xffffffffu, v[0], lm);
         v[0] = sel_minmax(lower, v[0], a);
       } else {
 #pragma unroll
         for (int r = 0; r < R / 2; ++r) {
-          T a = __shfl_xor_sync(0xffffffffu, v[R - 1 - r], lm);
-          T c = __shfl_xor_sync(0xffffffffu, v[r], lm);
+          const uint32_t a = __shfl_xor_sync(0xffffffffu, v[R - 1 - r], lm);
+          const uint32_t c = __shfl_xor_sync(0xffffffffu, v[r], lm);
           v[r] = sel_minmax(lower, v[r], a);
           v[R - 1 - r] = sel_minmax(lower, v[R - 1 - r], c);
         }
       }
     }
+#pragma unroll 1
+    for (unsigned jj = kk >> 1; jj >= 1; jj >>= 1) {
+      const bool lower = (lane & jj) == 0;
 #pragma unroll
-    for (int j = k >> 2; j >= 1; j >>= 1) {
-      if (j < R) {
+      for (int r = 0; r < R; ++r) {
+        const uint32_t a = __shfl_xor_sync(0xffffffffu, v[r], jj);
+        v[r] = sel_minmax(lower, v[r], a);
+      }
+    }
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const int pr = r ^ j;
-          if (pr > r) cex(v[r], v[pr]);
-        }
-      } else {
-        const unsigned lm = j / R;
-        const bool lower = (lane & lm) == 0;
+    for (int j = R >> 1; j >= 1; j >>= 1) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          T a = __shfl_xor_sync(0xffffffffu, v[r], lm);
-          v[r] = sel_minmax(lower, v[r], a);
-        }
+      for (int r = 0; r < R; ++r) {
+        const int pr = r ^ j;
+        if (pr > r) cex(v[r], v[pr]);
       }
     }
   }
 }
 
 // p-values: same expressions, same order as oracle/DECISIONS.md "p-values".
-__device__ double p_mann_whitney(long long u1x2, uint32_t n1, uint32_t n2, long long ties) {
+__device__ __noinline__ double p_mann_whitney(long long u1x2, uint32_t n1, uint32_t n2, long long ties) {
   double nn = (double)n1 * (double)n2, N = (double)n1 + (double)n2;
   double var = nn / 12.0 * ((N + 1.0) - (double)ties / (N * (N - 1.0)));
   if (!(var > 0.0)) return 1.0;
@@ -93,7 +107,7 @@ __device__ double p_mann_whitney(long long u1x2, uint32_t n1, uint32_t n2, long 
   return p > 1.0 ? 1.0 : p;
 }
 
-__device__ double p_kruskal(long long r1x2, uint32_t n1, uint32_t n2, long long ties, double *h_out) {
+__device__ __noinline__ double p_kruskal(long long r1x2, uint32_t n1, uint32_t n2, long long ties, double *h_out) {
   double N = (double)n1 + (double)n2;
   long long Ni = (long long)n1 + n2;
   long long r2x2 = Ni * (Ni + 1) - r1x2;
@@ -107,7 +121,7 @@ __device__ double p_kruskal(long long r1x2, uint32_t n1, uint32_t n2, long long 
   return erfc(sqrt(h * 0.5));
 }
 
-__device__ double p_wilcoxon(long long wp2, long long wm2, uint32_t n, long long ties) {
+__device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t n, long long ties) {
   if (n == 0) return 1.0;
   double nd = (double)n;
   double se2 = nd * (nd + 1.0) * (2.0 * nd + 1.0) / 24.0 - (double)ties / 48.0;
@@ -119,127 +133,193 @@ __device__ double p_wilcoxon(long long wp2, long long wm2, uint32_t n, long long
 }
 
 template <int R>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_rank(DevBatch b, const DevParams *__restrict__ dp,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, const DevParams *__restrict__ dp,
                                                               fm_series_score *__restrict__ scores) {
-  constexpr int kTile = 33 * R + 1;  // padded words per sorted run
-  __shared__ float s_tile[kWarpsPerBlock][2][kTile];
+  constexpr int kTile = 33 * R + 2;  // padded words per sorted run (+ one sentinel slot)
+  extern __shared__ uint32_t s_tiles[];  // [warps][2][kTile]: baseline keys, current keys (|d| keys borrow the 2nd)
 
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t pairwise = dp->pairwise;
   const bool want_mw = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_MANN_WHITE;
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
   const bool want_k = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_KRUSKAL;
-  float *const sA = s_tile[warp][0], *const sB = s_tile[warp][1];
-  uint32_t *const sK = reinterpret_cast<uint32_t *>(sA);
+  uint32_t *const sA = s_tiles + (size_t)warp * 2 * kTile, *const sB = sA + kTile;
 
-  for (uint64_t u = (uint64_t)blockIdx.x * kWarpsPerBlock + warp; u < b.n_units;
-       u += (uint64_t)gridDim.x * kWarpsPerBlock) {
-    const int64_t off = b.offsets[u];
-    const uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
+  // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
+  const uint64_t n_rounds = (b.n_units + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
+  for (uint64_t round = 0; round < n_rounds; ++round) {
+    const uint64_t u = (round * gridDim.x + blockIdx.x) * kWarpsPerBlock + warp;
+    const bool have = u < b.n_units;
+    int64_t off = 0;
+    uint32_t nh = 0, nb = 0, nc = 0;
+    if (have) {
+      off = b.offsets[u];
+      nh = b.seg_lens[3 * u]; nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2];
+    }
+    {  // pull the next round's samples towards L2 while this round sorts
+      const uint64_t un = u + (uint64_t)gridDim.x * kWarpsPerBlock;
+      if (un < b.n_units) {
+        const int64_t offn = b.offsets[un];
+        const uint32_t nhn = b.seg_lens[3 * un], len = b.seg_lens[3 * un + 1] + b.seg_lens[3 * un + 2];
+        const char *p = reinterpret_cast<const char *>(b.values + offn + nhn);
+        for (uint32_t byte = lane * 128; byte < len * 4 + 128; byte += 32 * 128)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
+      }
+    }
     const float *base = b.values + off + nh, *cur = base + nb;
     const uint32_t m = min(nb, nc);
     const bool fits = nb <= 32u * R && nc <= 32u * R;
-    const bool run_mw = want_mw && nb >= dp->min_mann_white && nc >= dp->min_mann_white && m > 0 && fits;
-    const bool run_w = want_w && m >= dp->min_wilcoxon && m > 0 && fits;
-    const bool run_k = want_k && nb >= dp->min_kruskal && nc >= dp->min_kruskal && m > 0 && fits;
+    const bool run_mw = have && want_mw && nb >= dp->min_mann_white && nc >= dp->min_mann_white && m > 0 && fits;
+    const bool run_w = have && want_w && m >= dp->min_wilcoxon && m > 0 && fits;
+    const bool run_k = have && want_k && nb >= dp->min_kruskal && nc >= dp->min_kruskal && m > 0 && fits;
+    const bool pooled = run_mw || run_k;
 
     long long w_2wp = 0, w_ties = 0, mw_2r1 = 0, mw_ties = 0;
     uint32_t w_n = 0;
+    bool ties_within = false;  // equal samples inside the baseline or inside the current segment
 
-    if (run_w) {
-      uint32_t key[R];
-      uint32_t nz = 0;
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const uint32_t e = r * 32 + lane;
-        uint32_t k = kKeySentinel;
-        if (e < m) {
-          const float d = cur[e] - base[e];
-          if (d != 0.0f) {
-            k = (__float_as_uint(fabsf(d)) << 1) | (d < 0.0f ? 1u : 0u);
-            ++nz;
-          }
-        }
-        key[r] = k;
-      }
-      w_n = __reduce_add_sync(0xffffffffu, nz);
-      warp_bitonic_sort<R, uint32_t>(key, lane);
-      __syncwarp();
-#pragma unroll
-      for (int r = 0; r < R; ++r) sK[fm_pidx(lane * R + r)] = key[r];
-      __syncwarp();
-      fm_w_lane(sK, (int)w_n, (int)lane, w_2wp, w_ties);
-      w_2wp = warp_sum_i64(w_2wp);
-      w_ties = warp_sum_i64(w_ties);
-      __syncwarp();
-    }
-    if (run_mw || run_k) {
+    // one sort routine, three passes: |d| keys (Wilcoxon), baseline, current
 #pragma unroll 1
-      for (int seg = 0; seg < 2; ++seg) {
-        const float *src = seg ? cur : base;
-        const uint32_t n = seg ? nc : nb;
-        float *dst = seg ? sB : sA;
-        float v[R];
+    for (int seg = 0; seg < 3; ++seg) {
+      if (seg == 0 ? !run_w : !pooled) continue;
+      uint32_t key[R];
+      uint32_t n_valid;
+      if (seg == 0) {
+        uint32_t nz = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const uint32_t e = r * 32 + lane;
-          v[r] = e < n ? src[e] : CUDART_INF_F;
+          uint32_t k = kKeySentinel;
+          if (e < m) {
+            const float d = cur[e] - base[e];
+            if (d != 0.0f) {
+              k = (__float_as_uint(fabsf(d)) << 1) | (d < 0.0f ? 1u : 0u);
+              ++nz;
+            }
+          }
+          key[r] = k;
         }
-        warp_bitonic_sort<R, float>(v, lane);
+        n_valid = w_n = __reduce_add_sync(0xffffffffu, nz);
+      } else {
+        const float *src = seg == 1 ? base : cur;
+        n_valid = seg == 1 ? nb : nc;
 #pragma unroll
-        for (int r = 0; r < R; ++r) dst[fm_pidx(lane * R + r)] = v[r];
+        for (int r = 0; r < R; ++r) {
+          const uint32_t e = r * 32 + lane;
+          key[r] = e < n_valid ? float_key(src[e]) : kKeySentinel;
+        }
       }
+      warp_bitonic_sort<R>(key, lane);
+
+      // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1)
+      const uint32_t sh = seg == 0 ? 1u : 0u;  // |d| keys carry the sign in bit 0
+      bool tie = false;
+#pragma unroll
+      for (int r = 0; r + 1 < R; ++r)
+        tie = tie || (((key[r] >> sh) == (key[r + 1] >> sh)) && (lane * R + r + 1 < n_valid));
+      const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1);
+      tie = tie || (lane < 31 && ((key[R - 1] >> sh) == (nxt >> sh)) && (lane * R + R < n_valid));
+      const bool any_tie = __any_sync(0xffffffffu, tie);
+
+      if (seg == 0 && !any_tie) {
+        // tie-free |d|: the rank of sorted position e is e+1, no shared memory needed
+        int acc = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const uint32_t e = lane * R + r;
+          if (e < n_valid && !(key[r] & 1u)) acc += 2 * (int)(e + 1);
+        }
+        w_2wp = __reduce_add_sync(0xffffffffu, (uint32_t)acc);
+      } else {
+        uint32_t *dst = seg == 1 ? sA : sB;
+#pragma unroll
+        for (int r = 0; r < R; ++r) dst[fm_pidx(lane * R + r)] = key[r];
+        if (lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
+        if (seg == 0) {
+          __syncwarp();
+          fm_w_lane(sB, (int)w_n, (int)lane, w_2wp, w_ties);
+          w_2wp = warp_sum_i64(w_2wp);
+          w_ties = warp_sum_i64(w_ties);
+          __syncwarp();
+        } else {
+          ties_within = ties_within || any_tie;
+        }
+      }
+    }
+    if (pooled) {
       __syncwarp();
-      fm_mw_lane(sA, (int)nb, sB, (int)nc, (int)lane, mw_2r1, mw_ties);
-      mw_2r1 = warp_sum_i64(mw_2r1);
-      mw_ties = warp_sum_i64(mw_ties);
+      bool slow = ties_within;
+      if (!slow) {
+        int plt;
+        const bool cross = fm_mw_lane_fast(sA, (int)nb, sB, (int)nc, (int)lane, plt);
+        slow = __any_sync(0xffffffffu, cross);
+        if (!slow) mw_2r1 = (long long)nb * ((long long)nb + 1) + 2ll * (long long)__reduce_add_sync(0xffffffffu, (uint32_t)plt);
+      }
+      if (slow) {
+        fm_mw_lane(sA, (int)nb, sB, (int)nc, (int)lane, mw_2r1, mw_ties);
+        mw_2r1 = warp_sum_i64(mw_2r1);
+        mw_ties = warp_sum_i64(mw_ties);
+      }
       __syncwarp();
     }
 
-    // ---- p-values on lanes 0..2, combiner on lane 0
-    const long long mw_2u1 = mw_2r1 - (long long)nb * ((long long)nb + 1);
-    const long long w_2wm = (long long)w_n * ((long long)w_n + 1) - w_2wp;
-    double p = 1.0, kw_h = 0.0;
-    if (lane == 0 && run_mw) p = p_mann_whitney(mw_2u1, nb, nc, mw_ties);
-    if (lane == 1 && run_w) p = p_wilcoxon(w_2wp, w_2wm, w_n, w_ties);
-    if (lane == 2 && run_k) p = p_kruskal(mw_2r1, nb, nc, mw_ties, &kw_h);
-    const double p_mw = __shfl_sync(0xffffffffu, p, 0), p_w = __shfl_sync(0xffffffffu, p, 1);
-    const double p_k = __shfl_sync(0xffffffffu, p, 2);
-    kw_h = __shfl_sync(0xffffffffu, kw_h, 2);
-    if (lane == 0) {
-      const double alpha = dp->pairwise_threshold;
-      const int n_run = (int)run_mw + (int)run_w + (int)run_k;
-      const int n_rej = (int)(run_mw && p_mw < alpha) + (int)(run_w && p_w < alpha) + (int)(run_k && p_k < alpha);
-      bool differs = false;
-      if (pairwise == FM_PW_ALL) differs = n_run > 0 && n_rej == n_run;
-      else if (pairwise != FM_PW_NONE) differs = n_rej > 0;
-      uint32_t status = (differs ? FM_S_DIFFERS : 0u) | (run_mw ? FM_S_MW_RUN : 0u) |
-                        (run_w ? FM_S_WILCOXON_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u);
+    // ---- exact integer statistics out; p-values and the combiner run one thread per unit in
+    //      k_rank_finalize (three lanes of a warp doing erfc here cost a third of the kernel's
+    //      instruction footprint for 3/32 of its lanes)
+    if (lane == 0 && have) {
       fm_series_score *o = scores + u;
-      o->status = status;
+      o->status = (run_mw ? FM_S_MW_RUN : 0u) | (run_w ? FM_S_WILCOXON_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u);
       o->w_n = w_n;
-      const bool pooled = run_mw || run_k;
-      o->mw_2u1 = pooled ? mw_2u1 : 0;
+      o->mw_2u1 = pooled ? mw_2r1 - (long long)nb * ((long long)nb + 1) : 0;
       o->mw_2r1 = pooled ? mw_2r1 : 0;
       o->mw_ties = pooled ? mw_ties : 0;
       o->w_2wplus = w_2wp;
-      o->w_2wminus = run_w ? w_2wm : 0;
+      o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
       o->w_ties = w_ties;
-      o->p_mw = p_mw;
-      o->p_w = p_w;
-      o->p_k = p_k;
-      o->kw_h = kw_h;
     }
   }
+}
+
+// One thread per unit: normal-approximation p-values and the ALL/ANY combiner
+// (ML_PAIRWISE_ALGORITHM / ML_PAIRWISE_THRESHOLD, foremast-brain/README.md:34-35).
+__global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevParams *__restrict__ dp,
+                                                        fm_series_score *__restrict__ scores) {
+  const uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= b.n_units) return;
+  fm_series_score *o = scores + u;
+  const uint32_t st = o->status, nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
+  const bool run_mw = st & FM_S_MW_RUN, run_w = st & FM_S_WILCOXON_RUN, run_k = st & FM_S_KRUSKAL_RUN;
+  double p_mw = 1.0, p_w = 1.0, p_k = 1.0, kw_h = 0.0;
+  if (run_mw) p_mw = p_mann_whitney(o->mw_2u1, nb, nc, o->mw_ties);
+  if (run_w) p_w = p_wilcoxon(o->w_2wplus, o->w_2wminus, o->w_n, o->w_ties);
+  if (run_k) p_k = p_kruskal(o->mw_2r1, nb, nc, o->mw_ties, &kw_h);
+  const double alpha = dp->pairwise_threshold;
+  const uint32_t pairwise = dp->pairwise;
+  const int n_run = (int)run_mw + (int)run_w + (int)run_k;
+  const int n_rej = (int)(run_mw && p_mw < alpha) + (int)(run_w && p_w < alpha) + (int)(run_k && p_k < alpha);
+  bool differs = false;
+  if (pairwise == FM_PW_ALL) differs = n_run > 0 && n_rej == n_run;
+  else if (pairwise != FM_PW_NONE) differs = n_rej > 0;
+  if (differs) o->status = st | FM_S_DIFFERS;
+  o->p_mw = p_mw;
+  o->p_w = p_w;
+  o->p_k = p_k;
+  o->kw_h = kw_h;
 }
 
 template <int R>
 cudaError_t launch(const DevBatch &b, const DevParams *dp, fm_series_score *scores, int sm_count, cudaStream_t st) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  const uint64_t cap = (uint64_t)sm_count * 64;  // grid-stride beyond a few waves
+    // many more blocks than are resident: tie-heavy units take longer, the block scheduler evens it
+  // out (a persistent 5-blocks-per-SM grid measured 19 % slower)
+  const uint64_t cap = (uint64_t)sm_count * 64;
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  k_rank<R><<<(unsigned)blocks, kWarpsPerBlock * 32, 0, st>>>(b, dp, scores);
+  constexpr int smem = kWarpsPerBlock * 2 * (33 * R + 2) * 4;
+  cudaError_t e = cudaFuncSetAttribute(k_rank<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  k_rank<R><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
+  k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
   return cudaGetLastError();
 }
 

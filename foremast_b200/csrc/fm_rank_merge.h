@@ -13,8 +13,10 @@
 
 #ifdef __CUDACC__
 #define FM_HD __host__ __device__ __forceinline__
+#define FM_HD_COLD __host__ __device__ __noinline__  // tie-group slow path: keep it out of the hot footprint
 #else
 #define FM_HD inline
+#define FM_HD_COLD inline
 #endif
 
 // shared-memory index of sorted element e: one pad word per 32 keeps the warp's post-sort
@@ -24,7 +26,7 @@ FM_HD int fm_pidx(int e) { return e + (e >> 5); }
 // a[start..n) is sorted; returns the first index >= start whose element differs from v
 // (start itself if a[start] != v).  Gallop + binary search: O(log run length).
 template <typename T>
-FM_HD int fm_run_end(const T *a, int n, int start, T v) {
+FM_HD_COLD int fm_run_end(const T *a, int n, int start, T v) {
   int e = start;
   if (e < n && a[fm_pidx(e)] == v) {
     int step = 1;
@@ -39,8 +41,9 @@ FM_HD int fm_run_end(const T *a, int n, int start, T v) {
   return e;
 }
 
-// Mann-Whitney / Kruskal-Wallis share this: A = sorted baseline (na), B = sorted current (nb).
-FM_HD void fm_mw_lane(const float *A, int na, const float *B, int nb, int lane, long long &r2, long long &ties) {
+// Mann-Whitney / Kruskal-Wallis share this: A = sorted baseline (na), B = sorted current (nb),
+// both as order-preserving u32 keys of the fp32 samples.
+FM_HD_COLD void fm_mw_lane(const uint32_t *A, int na, const uint32_t *B, int nb, int lane, long long &r2, long long &ties) {
   const int n = na + nb, c = (n + 31) >> 5;
   int p0 = lane * c;
   if (p0 > n) p0 = n;
@@ -57,9 +60,9 @@ FM_HD void fm_mw_lane(const float *A, int na, const float *B, int nb, int lane, 
   }
   int i = lo, j = p0 - lo;
   if (p0 > 0) {  // a group that started in an earlier span belongs to that lane: skip its tail
-    float prev;
+    uint32_t prev;
     if (i > 0 && j > 0) {
-      float x = A[fm_pidx(i - 1)], y = B[fm_pidx(j - 1)];
+      uint32_t x = A[fm_pidx(i - 1)], y = B[fm_pidx(j - 1)];
       prev = x > y ? x : y;
     } else if (i > 0) prev = A[fm_pidx(i - 1)];
     else prev = B[fm_pidx(j - 1)];
@@ -67,9 +70,9 @@ FM_HD void fm_mw_lane(const float *A, int na, const float *B, int nb, int lane, 
     j = fm_run_end(B, nb, j, prev);
   }
   while (i + j < p1) {
-    float v;
+    uint32_t v;
     if (i < na && j < nb) {
-      float x = A[fm_pidx(i)], y = B[fm_pidx(j)];
+      uint32_t x = A[fm_pidx(i)], y = B[fm_pidx(j)];
       v = x < y ? x : y;
     } else if (i < na) v = A[fm_pidx(i)];
     else v = B[fm_pidx(j)];
@@ -82,8 +85,44 @@ FM_HD void fm_mw_lane(const float *A, int na, const float *B, int nb, int lane, 
   }
 }
 
+// Fast path of fm_mw_lane for tie-free data (continuous metrics): one balanced merge walk with a
+// uniform trip count and no group bookkeeping.  plt accumulates, over the baseline samples taken
+// in this lane's span, how many current samples are smaller; without ties
+// 2*R1 = na*(na+1) + 2*sum(plt) and the tie term is 0.  Returns true if a baseline and a current
+// sample compare equal anywhere in the span (then the caller must use fm_mw_lane instead).
+// Both runs must be followed by the 0xFFFFFFFF sentinel (index na / nb readable).
+FM_HD bool fm_mw_lane_fast(const uint32_t *A, int na, const uint32_t *B, int nb, int lane, int &plt) {
+  const int n = na + nb, c = (n + 31) >> 5;
+  int p0 = lane * c;
+  if (p0 > n) p0 = n;
+  int p1 = p0 + c;
+  if (p1 > n) p1 = n;
+  plt = 0;
+  if (p0 >= p1) return false;
+  int lo = p0 > nb ? p0 - nb : 0, hi = p0 < na ? p0 : na;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (A[fm_pidx(mid)] <= B[fm_pidx(p0 - 1 - mid)]) lo = mid + 1; else hi = mid;
+  }
+  int i = lo, j = p0 - lo;
+  uint32_t ha = A[fm_pidx(i)], hb = B[fm_pidx(j)];
+  bool tie = false;
+  for (int p = p0; p < p1; ++p) {
+    tie = tie || (ha == hb);  // both heads real here: at most one run is exhausted before p1
+    if (ha <= hb) {           // baseline first on ties
+      plt += j;
+      ++i;
+      ha = A[fm_pidx(i)];
+    } else {
+      ++j;
+      hb = B[fm_pidx(j)];
+    }
+  }
+  return tie;
+}
+
 // Wilcoxon signed-rank: K = sorted keys (|d| bits << 1 | (d < 0)), n = number of non-zero pairs.
-FM_HD void fm_w_lane(const uint32_t *K, int n, int lane, long long &wp2, long long &ties) {
+FM_HD_COLD void fm_w_lane(const uint32_t *K, int n, int lane, long long &wp2, long long &ties) {
   const int c = (n + 31) >> 5;
   int p0 = lane * c;
   if (p0 > n) p0 = n;

@@ -58,15 +58,16 @@ static float sample(const fm_synth_config *cfg, uint64_t gu, uint32_t mt, u32x4 
   float drift = (u01(r.v[1]) - 0.5f) * base_m * 1.0e-5f;
   u32x4 q = philox4x32_10((uint32_t)gu, (uint32_t)(gu >> 32), t, 0xBu, cfg->seed, 0x466F7265u);
   float noise = (((u01(q.v[0]) + u01(q.v[1])) + (u01(q.v[2]) + u01(q.v[3]))) - 2.0f) * 1.7320508f;
+  noise = fminf(1.25f, fmaxf(-1.25f, noise));  /* bounded noise: k >= 2 bands stay quiet without an injected anomaly */
   float ph = (float)(t % 1440u) * (1.0f / 1440.0f) + phi;
   ph = ph - floorf(ph);
   float tri = 1.0f - 4.0f * fabsf(ph - 0.5f);
-  float season = base_m * (1.0f + 0.3f * tri);
+  float season = base_m * (1.0f + 0.02f * tri);
   float x = season + drift * (float)t;
   x = x + sigma_m * noise;
   if (in_cur && (cfg->flags & FM_SYNTH_ANOMALIES)) {
-    if (r.v[2] % 100u == 0u && cfg->n_cur > 0 && cur_idx == r.v[3] % cfg->n_cur) x = x * 20.0f + 5.0f * base_m;
-    if (r.v[2] % 200u == 1u) x = x * 1.5f + sigma_m;
+    if (r.v[2] % 400u == 0u && cfg->n_cur > 0 && cur_idx == r.v[3] % cfg->n_cur) x = x * 20.0f + 5.0f * base_m;
+    if (r.v[2] % 800u == 1u) x = x * 1.5f + sigma_m;
   }
   if (!(x > 0.0f)) x = 0.0f;
   if (mt == FM_MT_ERROR5XX || mt == FM_MT_ERROR4XX) x = rintf(x * 1000.0f) * 0.001f;
