@@ -554,8 +554,7 @@ static void result_release(fm_result *r) {
 
 static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
   if (p->algorithms & ~FM_ALG_ALL) return set_err(ctx, FM_E_INVALID, "unknown algorithm bits");
-  if (p->algorithms & (FM_ALG_MA_ROLLING | FM_ALG_HW))
-    return set_err(ctx, FM_E_UNSUPPORTED, "FM_ALG_MA_ROLLING / FM_ALG_HW are not built yet");
+  if (p->algorithms & FM_ALG_HW) return set_err(ctx, FM_E_UNSUPPORTED, "FM_ALG_HW is not built yet");
   if (p->pairwise > FM_PW_KRUSKAL) return set_err(ctx, FM_E_INVALID, "unknown pairwise algorithm");
   if (p->band_algorithm && (!(p->band_algorithm & p->algorithms) || (p->band_algorithm & (p->band_algorithm - 1))))
     return set_err(ctx, FM_E_INVALID, "band_algorithm must be one enabled FM_ALG_* bit");

@@ -38,7 +38,23 @@ struct State {
   double es, esse, esig;
   // DES
   double dl, db, dsse, dsig;
-  uint32_t cnt[3], first[3];
+  // MA_ROLLING: running prefix sums of d and d*d (rp*) and the same sums W samples behind (rq*)
+  double rp1, rp2, rq1, rq2, rsd;
+  uint32_t cnt[4], first[4];  // MA_ALL, EWMA, DES, MA_ROLLING
+};
+
+// One sample of the stream W positions back, for the lagging prefix sums of the rolling band.
+// Read straight from global memory: the line was fetched by the main stream moments ago and sits
+// in L1/L2, so this costs no HBM traffic.
+struct Lag {
+  const float *unit;   // values + offset of this unit
+  uint32_t a0, ns, c0, W;
+  __device__ __forceinline__ bool at(uint32_t q, double &x) const {
+    if (q < W) return false;
+    const uint32_t sp = q - W;
+    x = (double)__ldg(unit + (sp < ns ? a0 + sp : c0 + (sp - ns)));
+    return true;
+  }
 };
 
 __device__ __forceinline__ bool outside(double x, double up, double lo, uint32_t bound) {
@@ -46,7 +62,22 @@ __device__ __forceinline__ bool outside(double x, double up, double lo, uint32_t
 }
 
 template <uint32_t ALGS>
-__device__ __forceinline__ void src_update(State<ALGS> &s, double xd, double alpha, double ab) {
+__device__ __forceinline__ void roll_advance(State<ALGS> &s, double xd, uint32_t q, const Lag &lag, bool valid) {
+  const double d = xd - s.x0;
+  s.rp1 += d;
+  s.rp2 = fma(d, d, s.rp2);
+  double xl;
+  if (valid && lag.at(q, xl)) {  // lanes riding along in a warp-uniform fast path must not touch memory
+    const double dq = xl - s.x0;
+    s.rq1 += dq;
+    s.rq2 = fma(dq, dq, s.rq2);
+  }
+}
+
+template <uint32_t ALGS>
+__device__ __forceinline__ void src_update(State<ALGS> &s, double xd, double alpha, double ab, uint32_t q, const Lag &lag,
+                                           bool valid) {
+  if (ALGS & FM_ALG_MA_ROLLING) roll_advance<ALGS>(s, xd, q, lag, valid);
   if (ALGS & FM_ALG_MA_ALL) {
     double d = xd - s.x0;
     s.s1 += d;
@@ -85,7 +116,23 @@ __device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t
 // One current point: flag against each band, then keep the smoothers running (D4).
 template <uint32_t ALGS>
 __device__ __forceinline__ void cur_update(State<ALGS> &s, const Rule &r, double xd, uint32_t j, bool valid,
-                                           double alpha, double ab, float &bup, float &blo, uint32_t band_alg) {
+                                           double alpha, double ab, float &bup, float &blo, uint32_t band_alg,
+                                           const Lag &lag) {
+  if (ALGS & FM_ALG_MA_ROLLING) {
+    const uint32_t q = lag.ns + j, cnt = lag.W < q ? lag.W : q;
+    const double a1 = s.rp1 - s.rq1, a2 = s.rp2 - s.rq2;
+    const double m1 = a1 / (double)cnt, mean = s.x0 + m1;
+    double var = fma(-m1, m1, a2 / (double)cnt);
+    if (!(var > 0.0)) var = 0.0;
+    const double sd = sqrt(var), up = fma(r.k, sd, mean);
+    double lo = fma(-r.k, sd, mean);
+    lo = lo < r.mlb ? r.mlb : lo;
+    if (valid) s.rsd = sd;
+    const bool f = valid && outside(xd, up, lo, r.bound);
+    if (f && s.cnt[3]++ == 0) s.first[3] = j;
+    if (band_alg == FM_ALG_MA_ROLLING) { bup = (float)up; blo = (float)lo; }
+    roll_advance<ALGS>(s, xd, q, lag, valid);
+  }
   if (ALGS & FM_ALG_MA_ALL) {
     bool f = valid && outside(xd, s.ma_up, s.ma_lo, r.bound);
     if (f && s.cnt[0]++ == 0) s.first[0] = j;
@@ -161,8 +208,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   s.x0 = s.s1 = s.s2 = s.ma_up = s.ma_lo = s.ma_mean = s.ma_sd = 0.0;
   s.es = s.esse = s.esig = 0.0;
   s.dl = s.db = s.dsse = s.dsig = 0.0;
+  s.rp1 = s.rp2 = s.rq1 = s.rq2 = s.rsd = 0.0;
 #pragma unroll
-  for (int a = 0; a < 3; ++a) { s.cnt[a] = 0; s.first[a] = FM_NONE_IDX; }
+  for (int a = 0; a < 4; ++a) { s.cnt[a] = 0; s.first[a] = FM_NONE_IDX; }
+  Lag lag;
+  lag.unit = b.values + off;
+  lag.a0 = a0; lag.ns = ns; lag.c0 = c0;
+  lag.W = active ? dp->ma_window : 0xFFFFFFFFu;  // lanes without a unit never touch memory
 
   // ---- staging set-up
   s_off[lane] = off;
@@ -206,10 +258,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
 #pragma unroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
-        src_update<ALGS>(s, (double)x.x, alpha, ab);
-        src_update<ALGS>(s, (double)x.y, alpha, ab);
-        src_update<ALGS>(s, (double)x.z, alpha, ab);
-        src_update<ALGS>(s, (double)x.w, alpha, ab);
+        const uint32_t q = cs + v4 * 4 - a0;
+        src_update<ALGS>(s, (double)x.x, alpha, ab, q + 0, lag, cls_src);
+        src_update<ALGS>(s, (double)x.y, alpha, ab, q + 1, lag, cls_src);
+        src_update<ALGS>(s, (double)x.z, alpha, ab, q + 2, lag, cls_src);
+        src_update<ALGS>(s, (double)x.w, alpha, ab, q + 3, lag, cls_src);
       }
     } else if (!BANDS && __all_sync(0xffffffffu, cls_cur || dontcare)) {
       float du, dl;
@@ -217,10 +270,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t j = cs + v4 * 4 - c0;
-        cur_update<ALGS>(s, r, (double)x.x, j + 0, cls_cur, alpha, ab, du, dl, 0u);
-        cur_update<ALGS>(s, r, (double)x.y, j + 1, cls_cur, alpha, ab, du, dl, 0u);
-        cur_update<ALGS>(s, r, (double)x.z, j + 2, cls_cur, alpha, ab, du, dl, 0u);
-        cur_update<ALGS>(s, r, (double)x.w, j + 3, cls_cur, alpha, ab, du, dl, 0u);
+        cur_update<ALGS>(s, r, (double)x.x, j + 0, cls_cur, alpha, ab, du, dl, 0u, lag);
+        cur_update<ALGS>(s, r, (double)x.y, j + 1, cls_cur, alpha, ab, du, dl, 0u, lag);
+        cur_update<ALGS>(s, r, (double)x.z, j + 2, cls_cur, alpha, ab, du, dl, 0u, lag);
+        cur_update<ALGS>(s, r, (double)x.w, j + 3, cls_cur, alpha, ab, du, dl, 0u, lag);
       }
     } else if (!__all_sync(0xffffffffu, cls_skip)) {
       // generic path: chunk straddles a segment edge for at least one lane
@@ -233,14 +286,16 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
               s.x0 = xd; s.s1 = 0.0; s.s2 = 0.0;
               s.es = xd; s.esse = 0.0;
               s.dl = xd; s.db = 0.0; s.dsse = 0.0;
+              s.rp1 = 0.0; s.rp2 = 0.0; s.rq1 = 0.0; s.rq2 = 0.0;
+              if (ALGS & FM_ALG_MA_ROLLING) roll_advance<ALGS>(s, xd, 0u, lag, true);  // d = 0 like the oracle's first step
             } else {
               if (t == a0 + 1) s.db = xd - s.dl;
-              src_update<ALGS>(s, xd, alpha, ab);
+              src_update<ALGS>(s, xd, alpha, ab, t - a0, lag, true);
             }
           } else if (t >= c0 && t < c1) {
             if (t == c0) finalize<ALGS>(s, r, ns);
             float bu = 0.f, bl = 0.f;
-            cur_update<ALGS>(s, r, xd, t - c0, true, alpha, ab, bu, bl, band_alg);
+            cur_update<ALGS>(s, r, xd, t - c0, true, alpha, ab, bu, bl, band_alg, lag);
             if (BANDS && band_alg) { band_up[off + t] = bu; band_lo[off + t] = bl; }
           }
         }
@@ -269,6 +324,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
         o->n_anom[2] = s.cnt[1]; o->first_idx[2] = s.first[1]; o->sigma[2] = s.esig;
         if (s.cnt[1] > 0 && s.cnt[1] >= min_pts) status |= FM_S_ANOMALY;
         pts = max(pts, s.cnt[1]);
+      }
+      if (ALGS & FM_ALG_MA_ROLLING) {
+        status |= 1u << (FM_S_ALG_SHIFT + 1);
+        o->n_anom[1] = s.cnt[3]; o->first_idx[1] = s.first[3]; o->sigma[1] = s.rsd;
+        if (s.cnt[3] > 0 && s.cnt[3] >= min_pts) status |= FM_S_ANOMALY;
+        pts = max(pts, s.cnt[3]);
       }
       if ((ALGS & FM_ALG_DES) && ns >= 2) {
         status |= 1u << (FM_S_ALG_SHIFT + 3);
@@ -306,22 +367,17 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_ser
 
 }  // namespace
 
-// algorithms: subset of {MA_ALL, EWMA, DES}; 0 still runs (it resolves unknown units and statuses).
+// algorithms: subset of {MA_ALL, MA_ROLLING, EWMA, DES}; 0 still runs (it resolves unknown units and statuses).
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
                            float *band_up, float *band_lo, cudaStream_t st) {
-  const uint32_t a = algorithms & (FM_ALG_MA_ALL | FM_ALG_EWMA | FM_ALG_DES);
+  const uint32_t a = algorithms & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES);
 #define FM_BAND_CASE(M) \
   case M: return launch<M>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo, st);
   switch (a) {
-    FM_BAND_CASE(0u)
-    FM_BAND_CASE(FM_ALG_MA_ALL)
-    FM_BAND_CASE(FM_ALG_EWMA)
-    FM_BAND_CASE(FM_ALG_DES)
-    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_EWMA)
-    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_DES)
-    FM_BAND_CASE(FM_ALG_EWMA | FM_ALG_DES)
-    FM_BAND_CASE(FM_ALG_MA_ALL | FM_ALG_EWMA | FM_ALG_DES)
+    FM_BAND_CASE(0u) FM_BAND_CASE(1u) FM_BAND_CASE(2u) FM_BAND_CASE(3u) FM_BAND_CASE(4u) FM_BAND_CASE(5u)
+    FM_BAND_CASE(6u) FM_BAND_CASE(7u) FM_BAND_CASE(8u) FM_BAND_CASE(9u) FM_BAND_CASE(10u) FM_BAND_CASE(11u)
+    FM_BAND_CASE(12u) FM_BAND_CASE(13u) FM_BAND_CASE(14u) FM_BAND_CASE(15u)
   }
 #undef FM_BAND_CASE
   return cudaErrorInvalidValue;

@@ -44,7 +44,7 @@ def assert_scores_equal(got, ref):
     return worst
 
 
-def full_params(oracle, algs=abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES, pairwise=abi.PW_ALL):
+def full_params(oracle, algs=abi.ALG_MA_ALL | abi.ALG_MA_ROLLING | abi.ALG_EWMA | abi.ALG_DES, pairwise=abi.PW_ALL):
     p = oracle.params_default()
     p.algorithms = algs
     p.pairwise = pairwise
@@ -132,10 +132,21 @@ def test_score_parity_on_synthetic_batches(ctx, oracle, shape, n):
 
 
 @pytest.mark.parametrize("pairwise", [abi.PW_NONE, abi.PW_ANY, abi.PW_MANN_WHITE, abi.PW_WILCOXON, abi.PW_KRUSKAL])
-@pytest.mark.parametrize("algs", [abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES, abi.ALG_MA_ALL | abi.ALG_DES])
+@pytest.mark.parametrize("algs", [abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES, abi.ALG_MA_ALL | abi.ALG_DES,
+                                  abi.ALG_MA_ROLLING, abi.ALG_MA_ROLLING | abi.ALG_EWMA])
 def test_parameter_combinations(ctx, oracle, pairwise, algs):
     b = ctx.batch_synth(1500, 200, 64, 64, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=7 + pairwise)
     p = full_params(oracle, algs, pairwise)
+    check_batch(ctx, oracle, b, p)
+    b.free()
+
+
+@pytest.mark.parametrize("window", [1, 7, 31, 32, 33, 100, 5000])
+def test_rolling_window_sizes(ctx, oracle, window):
+    """Rolling band for windows shorter / longer than a staging chunk, the model window and the unit."""
+    b = ctx.batch_synth(700, 150, 40, 70, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=window)
+    p = full_params(oracle, abi.ALG_MA_ROLLING, abi.PW_NONE)
+    p.ma_window = window
     check_batch(ctx, oracle, b, p)
     b.free()
 
@@ -203,8 +214,8 @@ def test_bulk_csr_ingest_and_realignment(ctx, oracle):
 def test_bands_materialised(ctx, oracle):
     b = ctx.batch_synth(200, 300, 0, 45, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
     host = b.download()
-    for alg in (abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES):
-        p = full_params(oracle, abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES, abi.PW_NONE)
+    for alg in (abi.ALG_MA_ALL, abi.ALG_MA_ROLLING, abi.ALG_EWMA, abi.ALG_DES):
+        p = full_params(oracle, abi.ALG_MA_ALL | abi.ALG_MA_ROLLING | abi.ALG_EWMA | abi.ALG_DES, abi.PW_NONE)
         p.band_algorithm = alg
         ref, up, lo = oracle.score(host, p, want_bands=True)
         res = ctx.score(b, p)
