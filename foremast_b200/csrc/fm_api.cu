@@ -103,6 +103,20 @@ void resolve_params(const fm_params *p, DevParams *d) {
   d->alpha = p->alpha;
   d->beta = p->beta;
   d->gamma = p->gamma;
+  {  // powers of the Holt-Winters level/trend transition matrix (fm_hw.cu)
+    const double a = p->alpha, ab = p->alpha * p->beta;
+    double A[4] = {1.0 - a, 1.0 - a, -ab, 1.0 - ab}, P[4] = {A[0], A[1], A[2], A[3]};
+    auto mul = [](const double *x, const double *y, double *o) {
+      const double r[4] = {x[0] * y[0] + x[1] * y[2], x[0] * y[1] + x[1] * y[3], x[2] * y[0] + x[3] * y[2], x[2] * y[1] + x[3] * y[3]};
+      for (int i = 0; i < 4; ++i) o[i] = r[i];
+    };
+    for (int l = 0; l < 32; ++l) {  // A^(l+1)
+      for (int i = 0; i < 4; ++i) d->hw_lane[4 * l + i] = P[i];
+      mul(P, A, P);
+    }
+    for (int i = 0; i < 5; ++i)
+      for (int j = 0; j < 4; ++j) d->hw_pow[4 * i + j] = d->hw_lane[4 * ((1 << i) - 1) + j];
+  }
   for (int i = 0; i < FM_MAX_METRIC_TYPES; ++i) {
     const fm_metric_rule &r = p->rules[i].bound ? p->rules[i] : p->rules[0];  // D16
     d->rules[i].threshold = r.threshold;
@@ -554,7 +568,8 @@ static void result_release(fm_result *r) {
 
 static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
   if (p->algorithms & ~FM_ALG_ALL) return set_err(ctx, FM_E_INVALID, "unknown algorithm bits");
-  if (p->algorithms & FM_ALG_HW) return set_err(ctx, FM_E_UNSUPPORTED, "FM_ALG_HW is not built yet");
+  if ((p->algorithms & FM_ALG_HW) && (p->period < 32 || p->period > 2048))
+    return set_err(ctx, FM_E_UNSUPPORTED, "Holt-Winters period must be between 32 and 2048 samples");
   if (p->pairwise > FM_PW_KRUSKAL) return set_err(ctx, FM_E_INVALID, "unknown pairwise algorithm");
   if (p->band_algorithm && (!(p->band_algorithm & p->algorithms) || (p->band_algorithm & (p->band_algorithm - 1))))
     return set_err(ctx, FM_E_INVALID, "band_algorithm must be one enabled FM_ALG_* bit");
@@ -605,8 +620,13 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   FM_R(cudaEventRecord(r->ev[1], st));
   if (do_rank) FM_R(fm_launch_rank(db, r->d_params, std::max(b->max_base, b->max_cur), r->d_scores, ctx->sm_count, st));
   FM_R(cudaEventRecord(r->ev[2], st));
+  const bool band_in_kband = (p->band_algorithm & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES)) != 0;
   FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, r->d_scores, r->d_unit_status, r->d_unit_points,
-                      r->d_band_up, r->d_band_lo, st));
+                      band_in_kband ? r->d_band_up : nullptr, band_in_kband ? r->d_band_lo : nullptr, st));
+  if (p->algorithms & FM_ALG_HW)
+    FM_R(fm_launch_hw(db, r->d_params, p->period, r->d_scores, r->d_unit_status, r->d_unit_points,
+                      p->band_algorithm == FM_ALG_HW ? r->d_band_up : nullptr,
+                      p->band_algorithm == FM_ALG_HW ? r->d_band_lo : nullptr, ctx->sm_count, st));
   FM_R(cudaEventRecord(r->ev[3], st));
   fm_launch_verdict_reduce(db, r->d_unit_status, r->d_unit_points, (uint32_t)ns, r->d_counts, r->d_worst, st);
   FM_R(cudaGetLastError());

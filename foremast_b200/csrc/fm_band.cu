@@ -218,9 +218,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
 
   // ---- staging set-up
   s_off[lane] = off;
-  s_len[lane] = active ? ((ntot + 3u) & ~3u) : 0u;   // inactive units are not even read
+  s_len[lane] = (active && ALGS) ? ((ntot + 3u) & ~3u) : 0u;   // inactive units are not even read
   __syncwarp();
-  const uint32_t nchunks = (warp_max_u32(active ? ntot : 0u) + kChunk - 1) / kChunk;
+  // with no band algorithm selected the kernel only resolves statuses: nothing is staged
+  const uint32_t nchunks = ALGS ? (warp_max_u32(active ? ntot : 0u) + kChunk - 1) / kChunk : 0u;
   const unsigned row_sub = lane >> 3, col4 = lane & 7;
 
   auto issue = [&](uint32_t ch) {

@@ -37,6 +37,9 @@ struct DevParams {
   uint32_t min_anomaly_points, ma_window, period, band_algorithm;
   double alpha, beta, gamma;
   DevRule rules[FM_MAX_METRIC_TYPES];
+  // Holt-Winters level/trend transition A = [[1-a, 1-a], [-ab, 1-ab]]: A^(2^i) and A^(lane+1), row-major
+  double hw_pow[5 * 4];
+  double hw_lane[32 * 4];
 };
 
 __device__ __forceinline__ unsigned fm_lane() { return threadIdx.x & 31u; }
@@ -69,6 +72,9 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t max_
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
                            float *band_up, float *band_lo, cudaStream_t st);
+cudaError_t fm_launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                         uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                         int sm_count, cudaStream_t st);
 void fm_launch_verdict_reduce(const DevBatch &b, const uint32_t *unit_status, const uint32_t *unit_points,
                               uint32_t n_services, uint32_t *counts, unsigned long long *worst, cudaStream_t st);
 void fm_launch_verdict_finalize(uint32_t n_services, const uint32_t *counts, const unsigned long long *worst,

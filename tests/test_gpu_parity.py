@@ -151,6 +151,34 @@ def test_rolling_window_sizes(ctx, oracle, window):
     b.free()
 
 
+@pytest.mark.parametrize("shape,period,n", [((400, 0, 90), 96, 600), ((10080, 0, 60), 1440, 150),
+                                            ((2900, 30, 1000), 1440, 100), ((64, 0, 33), 32, 300),
+                                            ((5000, 40, 40), 2048, 64)])
+def test_holt_winters(ctx, oracle, shape, period, n):
+    """BASELINE.json configs[3]: Holt-Winters seasonal (period 1440, 7-day history), continuous mode.
+    The kernel scans each 32-sample tile in parallel, so floats are compared at 1e-5 relative."""
+    b = ctx.batch_synth(n, *shape, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=period)
+    p = full_params(oracle, abi.ALG_HW | abi.ALG_MA_ALL, abi.PW_ALL)
+    p.period = period
+    got, worst = check_batch(ctx, oracle, b, p)
+    ran = (got["status"] >> (abi.S_ALG_SHIFT + 4)) & 1
+    assert ran.mean() > 0.9
+    print(f"HW shape={shape} period={period} worst rel err {worst:.3e}, anomalous {(got['n_anom'][:, 4] > 0).mean():.3f}")
+    # bands of the HW model
+    p.band_algorithm = abi.ALG_HW
+    host = b.download()
+    ref, up, lo = oracle.score(host, p, want_bands=True)
+    res = ctx.score(b, p)
+    for u in (0, n // 2, n - 1):
+        gu, gl = res.bands(u)
+        o = int(host.offsets[u]) + int(host.seg_lens[u][0]) + int(host.seg_lens[u][1])
+        if ran[u]:
+            np.testing.assert_allclose(gu, up[o:o + gu.size], rtol=1e-5)
+            np.testing.assert_allclose(gl, lo[o:o + gl.size], rtol=1e-5, atol=1e-30)
+    res.free()
+    b.free()
+
+
 def test_edge_cases(ctx, oracle):
     rng = np.random.default_rng(11)
     z = rng.normal(10, 1, 200).astype(np.float32)
