@@ -191,6 +191,25 @@ class Result:
         self.ctx._check(self.ctx._L.fm_result_bands(self._h, unit, up.ctypes.data, lo.ctypes.data, cap, C.byref(n)))
         return up[:n.value].copy(), lo[:n.value].copy()
 
+    def anomalies(self, algorithm):
+        """Compact anomaly list of one algorithm: (offsets[n_units+1], cur_idx[], values[])."""
+        total = C.c_uint64()
+        self.ctx._check(self.ctx._L.fm_result_anomalies_build(self._h, algorithm, C.byref(total)))
+        n = self.batch.info()["n_units"]
+        offsets = np.zeros(n + 1, np.uint64)
+        idx = np.zeros(total.value, np.uint32)
+        val = np.zeros(total.value, np.float32)
+        self.ctx._check(self.ctx._L.fm_result_anomalies_all(self._h, offsets.ctypes.data, idx.ctypes.data,
+                                                            val.ctypes.data, total.value))
+        return offsets, idx, val
+
+    def anomalies_unit(self, unit, cap=4096):
+        idx = np.zeros(cap, np.uint32)
+        val = np.zeros(cap, np.float32)
+        n = C.c_uint32()
+        self.ctx._check(self.ctx._L.fm_result_anomalies_unit(self._h, unit, idx.ctypes.data, val.ctypes.data, cap, C.byref(n)))
+        return idx[:n.value].copy(), val[:n.value].copy()
+
     def service_buffers(self):
         counts, worst, ns = C.c_void_p(), C.c_void_p(), C.c_uint32()
         self.ctx._check(self.ctx._L.fm_result_service_buffers(self._h, C.byref(counts), C.byref(worst), C.byref(ns)))

@@ -54,6 +54,13 @@ struct fm_result {
   unsigned long long *d_worst = nullptr;
   fm_verdict *d_verdicts = nullptr;
   float *d_band_up = nullptr, *d_band_lo = nullptr;
+  // compact anomaly list (fm_result_anomalies_build)
+  fm_params params;
+  unsigned long long *d_anom_off = nullptr;
+  uint32_t *d_anom_idx = nullptr;
+  float *d_anom_val = nullptr;
+  uint64_t anom_total = 0;
+  uint32_t anom_alg = 0;
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // start, pre-rank, post-rank, post-band, post-verdict
 };
 
@@ -558,7 +565,7 @@ void fm_batch_free(fm_batch *b) {
 static void result_release(fm_result *r) {
   cudaStream_t st = r->ctx->stream;
   void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts,
-                  r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo};
+                  r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo, r->d_anom_off, r->d_anom_idx, r->d_anom_val};
   for (void *p : ptrs)
     if (p) cudaFreeAsync(p, st);
   for (auto &e : r->ev)
@@ -584,6 +591,7 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   r->n_units = b->n_units;
   r->n_services = b->n_services;
   r->band_algorithm = p->band_algorithm;
+  r->params = *p;
   cudaStream_t st = ctx->stream;
   const uint64_t n = b->n_units, ns = b->n_services;
 #define FM_R(expr)                                                                              \
@@ -702,6 +710,83 @@ int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uin
     FM_CUDA(ctx, cudaMemcpyAsync(lower, r->d_band_lo + c0, seg[2] * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   }
+  return FM_OK;
+}
+
+// ---- compact anomaly list (a10)
+
+int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_points) {
+  if (!r) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  int a = -1;
+  for (int i = 0; i < FM_N_ALG; ++i)
+    if (algorithm == (1u << i)) a = i;
+  if (a < 0 || !(r->params.algorithms & algorithm))
+    return set_err(ctx, FM_E_INVALID, "algorithm must be one FM_ALG_* bit that was enabled in fm_score");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  for (void *p : {(void *)r->d_anom_off, (void *)r->d_anom_idx, (void *)r->d_anom_val})
+    if (p) cudaFreeAsync(p, st);
+  r->d_anom_off = nullptr; r->d_anom_idx = nullptr; r->d_anom_val = nullptr;
+  r->anom_total = 0; r->anom_alg = 0;
+  const uint64_t n = r->n_units;
+  unsigned long long *scratch = nullptr;
+  FM_CUDA(ctx, cudaMallocAsync(&r->d_anom_off, (n + 1) * sizeof(unsigned long long), st));
+  FM_CUDA(ctx, cudaMallocAsync(&scratch, fm_scan_scratch_bytes(n), st));
+  cudaError_t e = fm_launch_scan_counts(&r->d_scores->n_anom[a], sizeof(fm_series_score), n, r->d_anom_off, scratch, st);
+  unsigned long long total = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&total, r->d_anom_off + n, sizeof(total), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFreeAsync(scratch, st);
+  if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, FM_E_CUDA, std::string("anomaly offsets: ") + cudaGetErrorString(e)); }
+  FM_CUDA(ctx, cudaMallocAsync(&r->d_anom_idx, (total + 1) * sizeof(uint32_t), st));
+  FM_CUDA(ctx, cudaMallocAsync(&r->d_anom_val, (total + 1) * sizeof(float), st));
+  if (total) {
+    const DevBatch db = dev_view(r->batch);
+    if (algorithm == FM_ALG_HW)
+      FM_CUDA(ctx, fm_launch_hw_emit(db, r->d_params, r->params.period, r->d_scores, r->d_anom_off, r->d_anom_idx, r->d_anom_val, ctx->sm_count, st));
+    else
+      FM_CUDA(ctx, fm_launch_band_emit(db, r->d_params, algorithm, r->d_scores, r->d_anom_off, r->d_anom_idx, r->d_anom_val, st));
+    FM_CUDA(ctx, cudaStreamSynchronize(st));
+  }
+  r->anom_total = total;
+  r->anom_alg = algorithm;
+  if (n_points) *n_points = total;
+  return FM_OK;
+}
+
+int fm_result_anomalies_unit(fm_result *r, uint64_t unit, uint32_t *cur_idx, float *values, uint32_t cap, uint32_t *n) {
+  if (!r || !n) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  if (!r->d_anom_off) return set_err(ctx, FM_E_STATE, "call fm_result_anomalies_build first");
+  if (unit >= r->n_units) return set_err(ctx, FM_E_RANGE, "unit outside the batch");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  unsigned long long lim[2];
+  FM_CUDA(ctx, cudaMemcpyAsync(lim, r->d_anom_off + unit, sizeof(lim), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const uint64_t cnt = lim[1] - lim[0];
+  *n = (uint32_t)cnt;
+  if (cnt > cap) return set_err(ctx, FM_E_RANGE, "anomaly buffer too small");
+  if (cnt && cur_idx) FM_CUDA(ctx, cudaMemcpyAsync(cur_idx, r->d_anom_idx + lim[0], cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  if (cnt && values) FM_CUDA(ctx, cudaMemcpyAsync(values, r->d_anom_val + lim[0], cnt * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FM_OK;
+}
+
+int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, float *values, uint64_t cap) {
+  if (!r) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  if (!r->d_anom_off) return set_err(ctx, FM_E_STATE, "call fm_result_anomalies_build first");
+  if (cap < r->anom_total) return set_err(ctx, FM_E_RANGE, "anomaly buffer too small");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  if (offsets) FM_CUDA(ctx, cudaMemcpyAsync(offsets, r->d_anom_off, (r->n_units + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  if (r->anom_total && cur_idx) FM_CUDA(ctx, cudaMemcpyAsync(cur_idx, r->d_anom_idx, r->anom_total * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  if (r->anom_total && values) FM_CUDA(ctx, cudaMemcpyAsync(values, r->d_anom_val, r->anom_total * sizeof(float), cudaMemcpyDeviceToHost, st));
+  FM_CUDA(ctx, cudaStreamSynchronize(st));
   return FM_OK;
 }
 

@@ -159,12 +159,19 @@ __device__ __forceinline__ void cur_update(State<ALGS> &s, const Rule &r, double
   }
 }
 
-template <uint32_t ALGS, bool BANDS>
+// MODE 0: score.  MODE 1: score and materialise the per-point band of dp->band_algorithm.
+// MODE 2: emit pass of the anomaly list -- ALGS is one algorithm, only units with anomalies are
+// read again, and every flagged point is written to (emit_idx, emit_val) at emit_off[u] + k.
+template <uint32_t ALGS, int MODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const DevParams *__restrict__ dp,
                                                               bool rank_ran, fm_series_score *__restrict__ scores,
                                                               uint32_t *__restrict__ unit_status,
                                                               uint32_t *__restrict__ unit_points,
-                                                              float *__restrict__ band_up, float *__restrict__ band_lo) {
+                                                              float *__restrict__ band_up, float *__restrict__ band_lo,
+                                                              const unsigned long long *__restrict__ emit_off,
+                                                              uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val) {
+  constexpr bool BANDS = MODE == 1, EMIT = MODE == 2;
+  constexpr int kSlot = (ALGS & FM_ALG_MA_ALL) ? 0 : (ALGS & FM_ALG_EWMA) ? 1 : (ALGS & FM_ALG_DES) ? 2 : 3;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kStages * 32 * kRowWords);
@@ -180,7 +187,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     off = b.offsets[u];
     nh = b.seg_lens[3 * u]; nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2];
     mt = b.metric_type[u];
-    if (rank_ran) status = scores[u].status;
+    if (rank_ran || EMIT) status = scores[u].status;
+  }
+  unsigned long long emit_base = 0;
+  bool emit_any = true;
+  if (EMIT && have) {
+    emit_base = emit_off[u];
+    emit_any = emit_off[u + 1] > emit_base;
   }
   const uint32_t ntot = nh + nb + nc;
   // model window (D15)
@@ -188,7 +201,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   const uint32_t min_hist = dp->min_historical;
   if (nh >= min_hist && nh > 0) { a0 = 0; ns = nh; }
   else if (nb >= min_hist && nb > 0) { a0 = nh; ns = nb; status |= FM_S_MODEL_BASE; }
-  const bool active = have && ns > 0 && nc > 0;
+  const bool active = have && ns > 0 && nc > 0 && emit_any;
   if (have && !active) status |= FM_S_UNKNOWN;
   // ranges of this lane in unit coordinates; empty when inactive
   const uint32_t a1 = active ? a0 + ns : 0, c0 = active ? nh + nb : 0, c1 = active ? ntot : 0;
@@ -265,7 +278,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
         src_update<ALGS>(s, (double)x.z, alpha, ab, q + 2, lag, cls_src);
         src_update<ALGS>(s, (double)x.w, alpha, ab, q + 3, lag, cls_src);
       }
-    } else if (!BANDS && __all_sync(0xffffffffu, cls_cur || dontcare)) {
+    } else if (MODE == 0 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
       float du, dl;
 #pragma unroll
       for (int v4 = 0; v4 < 8; ++v4) {
@@ -296,8 +309,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
           } else if (t >= c0 && t < c1) {
             if (t == c0) finalize<ALGS>(s, r, ns);
             float bu = 0.f, bl = 0.f;
+            const uint32_t before = s.cnt[kSlot];
             cur_update<ALGS>(s, r, xd, t - c0, true, alpha, ab, bu, bl, band_alg, lag);
             if (BANDS && band_alg) { band_up[off + t] = bu; band_lo[off + t] = bl; }
+            if (EMIT && s.cnt[kSlot] != before) {
+              emit_idx[emit_base + before] = t - c0;
+              emit_val[emit_base + before] = row[i];
+            }
           }
         }
       }
@@ -306,7 +324,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   cp_async_wait<0>();
 
   // ---- results
-  if (have) {
+  if (have && !EMIT) {
     fm_series_score *o = scores + u;
     uint32_t pts = 0;
 #pragma unroll
@@ -347,23 +365,26 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   }
 }
 
-template <uint32_t ALGS>
-cudaError_t launch(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_series_score *scores,
-                   uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo, cudaStream_t st) {
+template <uint32_t ALGS, int MODE>
+cudaError_t launch_mode(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_series_score *scores,
+                        uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                        const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, cudaStream_t st) {
   const uint64_t per_block = kWarpsPerBlock * 32;
   const unsigned grid = (unsigned)((b.n_units + per_block - 1) / per_block);
   if (grid == 0) return cudaSuccess;
-  cudaError_t e;
-  if (band_up && band_lo) {
-    e = cudaFuncSetAttribute(k_band<ALGS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return e;
-    k_band<ALGS, true><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo);
-  } else {
-    e = cudaFuncSetAttribute(k_band<ALGS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return e;
-    k_band<ALGS, false><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points, nullptr, nullptr);
-  }
+  cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  k_band<ALGS, MODE><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points,
+                                                                    band_up, band_lo, emit_off, emit_idx, emit_val);
   return cudaGetLastError();
+}
+
+template <uint32_t ALGS>
+cudaError_t launch(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_series_score *scores,
+                   uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo, cudaStream_t st) {
+  if (band_up && band_lo)
+    return launch_mode<ALGS, 1>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo, nullptr, nullptr, nullptr, st);
+  return launch_mode<ALGS, 0>(b, dp, rank_ran, scores, unit_status, unit_points, nullptr, nullptr, nullptr, nullptr, nullptr, st);
 }
 
 }  // namespace
@@ -381,5 +402,19 @@ cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algo
     FM_BAND_CASE(12u) FM_BAND_CASE(13u) FM_BAND_CASE(14u) FM_BAND_CASE(15u)
   }
 #undef FM_BAND_CASE
+  return cudaErrorInvalidValue;
+}
+
+// Emit pass of the anomaly list for ONE algorithm of {MA_ALL, MA_ROLLING, EWMA, DES}: re-runs the
+// same deterministic recurrences over the units that have anomalies and writes each flagged
+// (current index, sample) at emit_off[u] + k.
+cudaError_t fm_launch_band_emit(const DevBatch &b, const DevParams *dp, uint32_t algorithm, fm_series_score *scores,
+                                const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, cudaStream_t st) {
+  switch (algorithm) {
+    case FM_ALG_MA_ALL: return launch_mode<FM_ALG_MA_ALL, 2>(b, dp, true, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, st);
+    case FM_ALG_MA_ROLLING: return launch_mode<FM_ALG_MA_ROLLING, 2>(b, dp, true, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, st);
+    case FM_ALG_EWMA: return launch_mode<FM_ALG_EWMA, 2>(b, dp, true, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, st);
+    case FM_ALG_DES: return launch_mode<FM_ALG_DES, 2>(b, dp, true, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, st);
+  }
   return cudaErrorInvalidValue;
 }

@@ -75,6 +75,14 @@ cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algo
 cudaError_t fm_launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
                          uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                          int sm_count, cudaStream_t st);
+cudaError_t fm_launch_band_emit(const DevBatch &b, const DevParams *dp, uint32_t algorithm, fm_series_score *scores,
+                                const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, cudaStream_t st);
+cudaError_t fm_launch_hw_emit(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                              const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
+                              cudaStream_t st);
+uint64_t fm_scan_scratch_bytes(uint64_t n);
+cudaError_t fm_launch_scan_counts(const void *in, size_t stride, uint64_t n, unsigned long long *out,
+                                  unsigned long long *scratch, cudaStream_t st);
 void fm_launch_verdict_reduce(const DevBatch &b, const uint32_t *unit_status, const uint32_t *unit_points,
                               uint32_t n_services, uint32_t *counts, unsigned long long *worst, cudaStream_t st);
 void fm_launch_verdict_finalize(uint32_t n_services, const uint32_t *counts, const unsigned long long *worst,

@@ -29,12 +29,16 @@ __device__ __forceinline__ V2 matvec(const double *m, V2 v) {  // m = {a00, a01,
   return r;
 }
 
-template <bool BANDS>
+// MODE 0 score, 1 score + bands, 2 emit pass of the anomaly list (see fm_band.cu)
+template <int MODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const DevParams *__restrict__ dp,
                                                             fm_series_score *__restrict__ scores,
                                                             uint32_t *__restrict__ unit_status,
                                                             uint32_t *__restrict__ unit_points,
-                                                            float *__restrict__ band_up, float *__restrict__ band_lo) {
+                                                            float *__restrict__ band_up, float *__restrict__ band_lo,
+                                                            const unsigned long long *__restrict__ emit_off,
+                                                            uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val) {
+  constexpr bool BANDS = MODE == 1, EMIT = MODE == 2;
   extern __shared__ double s_season[];  // [warps][period]
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t m = dp->period;
@@ -51,6 +55,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
     if (nh >= dp->min_historical && nh > 0) { a0 = 0; ns = nh; }
     else if (nb >= dp->min_historical && nb > 0) { a0 = nh; ns = nb; }
     if (ns == 0 || nc == 0 || (uint64_t)ns < 2ull * m) continue;  // unknown unit, or not two seasons of model window
+    unsigned long long emit_base = 0;
+    if (EMIT) {
+      emit_base = emit_off[u];
+      if (emit_off[u + 1] == emit_base) continue;
+    }
     const uint32_t c0 = nh + nb, n_stream = ns + nc;
     const float *unit = b.values + off;
     auto sample = [&](uint32_t q) -> double { return (double)unit[q < ns ? a0 + q : c0 + (q - ns)]; };
@@ -144,6 +153,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
           const unsigned fm = __ballot_sync(0xffffffffu, flag);
           if (fm) {
             if (n_anom == 0) first = (m + tile * 32 + (__ffs(fm) - 1)) - ns;
+            if (EMIT && flag) {
+              const unsigned long long at = emit_base + n_anom + __popc(fm & ((1u << lane) - 1u));
+              emit_idx[at] = q - ns;
+              emit_val[at] = (float)x;
+            }
             n_anom += __popc(fm);
           }
           if (BANDS && in_cur) {
@@ -160,7 +174,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
         __syncwarp();  // S[] written by this tile may be read by the next one when period < 64
       }
     }
-    if (lane == 0) {
+    if (lane == 0 && !EMIT) {
       fm_series_score *o = scores + u;
       st |= 1u << (FM_S_ALG_SHIFT + 4);
       if (n_anom > 0 && n_anom >= dp->min_anomaly_points) st |= FM_S_ANOMALY;
@@ -176,25 +190,35 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
 
 }  // namespace
 
-// Runs after fm_launch_band (it merges into the statuses that kernel wrote).  period must be in
-// [32, 2048]; the caller checks.
-cudaError_t fm_launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
-                         uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
-                         int sm_count, cudaStream_t st) {
+template <int MODE>
+static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                             uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                             const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
+                             cudaStream_t st) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const uint64_t cap = (uint64_t)sm_count * 32;
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
   const int smem = kWarpsPerBlock * (int)period * (int)sizeof(double);
-  cudaError_t e;
-  if (band_up && band_lo) {
-    e = cudaFuncSetAttribute(k_hw<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    k_hw<true><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo);
-  } else {
-    e = cudaFuncSetAttribute(k_hw<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    k_hw<false><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, nullptr, nullptr);
-  }
+  cudaError_t e = cudaFuncSetAttribute(k_hw<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  k_hw<MODE><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
+                                                               emit_off, emit_idx, emit_val);
   return cudaGetLastError();
+}
+
+// Runs after fm_launch_band (it merges into the statuses that kernel wrote).  period must be in
+// [32, 2048]; the caller checks.
+cudaError_t fm_launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                         uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                         int sm_count, cudaStream_t st) {
+  if (band_up && band_lo)
+    return launch_hw<1>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, nullptr, nullptr, nullptr, sm_count, st);
+  return launch_hw<0>(b, dp, period, scores, unit_status, unit_points, nullptr, nullptr, nullptr, nullptr, nullptr, sm_count, st);
+}
+
+cudaError_t fm_launch_hw_emit(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                              const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
+                              cudaStream_t st) {
+  return launch_hw<2>(b, dp, period, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, sm_count, st);
 }

@@ -260,6 +260,14 @@ int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_serie
 /* upper/lower band of the current segment of one unit, for the foremastbrain:*_upper/_lower
  * gauges (foremast-dashboard/src/config/metrics.js:20-31).  Needs params.band_algorithm. */
 int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uint32_t cap, uint32_t *n);
+/* Compact list of the anomalous current points of ONE algorithm, the device-side form of the
+ * anomaly pairs barrelman decodes as [t0, v0, t1, v1, ...]
+ * (foremast-barrelman/pkg/controller/DeploymentController.go:443-452; t = current start + idx*step).
+ * build: per-unit counts -> exclusive scan -> one emit pass over the units that have anomalies. */
+int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_points);
+int fm_result_anomalies_unit(fm_result *r, uint64_t unit, uint32_t *cur_idx, float *values, uint32_t cap, uint32_t *n);
+/* offsets has n_units+1 entries; cur_idx / values have room for cap >= n_points entries. */
+int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, float *values, uint64_t cap);
 /* Device pointers of the dense per-service counters, for the cross-GPU merge:
  * counts = uint32[4*n_services] (n_units, n_unknown, n_anom_units, n_anom_points), summed;
  * worst  = uint64[n_services]   ((points << 32) | ~unit), maxed. */

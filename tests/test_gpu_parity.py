@@ -258,6 +258,47 @@ def test_bands_materialised(ctx, oracle):
     b.free()
 
 
+@pytest.mark.parametrize("alg", [abi.ALG_MA_ALL, abi.ALG_MA_ROLLING, abi.ALG_EWMA, abi.ALG_DES, abi.ALG_HW])
+def test_anomaly_list(ctx, oracle, alg):
+    """Compact (index, value) list of the flagged current points (the [t0, v0, t1, v1, ...] pairs of
+    DeploymentController.go:443-452): recomputed on the host from the oracle's bands."""
+    n = 5000
+    b = ctx.batch_synth(n, 220, 0, 70, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=alg)
+    p = full_params(oracle, abi.ALG_ALL, abi.PW_NONE)
+    p.period = 48
+    p.band_algorithm = alg
+    host = b.download()
+    ref, up, lo = oracle.score(host, p, want_bands=True)
+    p.band_algorithm = 0
+    res = ctx.score(b, p)
+    a = {1: 0, 2: 1, 4: 2, 8: 3, 16: 4}[alg]
+    offsets, idx, val = res.anomalies(alg)
+    got = res.series()
+    assert np.array_equal(np.diff(offsets.astype(np.int64)), got["n_anom"][:, a])
+    assert int(offsets[-1]) == int(got["n_anom"][:, a].sum()) > 0
+    checked = 0
+    for u in np.flatnonzero(got["n_anom"][:, a])[:400]:
+        rule = p.rules[int(host.metric_type[u])] if p.rules[int(host.metric_type[u])].bound else p.rules[0]
+        cur = host.segments(u)[2]
+        o = int(host.offsets[u]) + int(host.seg_lens[u][0]) + int(host.seg_lens[u][1])
+        ub, lb = up[o:o + cur.size], lo[o:o + cur.size]
+        flags = ((rule.bound & 1) != 0) & (cur > ub) | ((rule.bound & 2) != 0) & (cur < lb)
+        # float32 bands can tie with the sample where the fp64 comparison does not; the counts are
+        # the exact ones, so only check the list against them and against unambiguous points
+        sl = slice(int(offsets[u]), int(offsets[u + 1]))
+        assert np.all(np.diff(idx[sl].astype(np.int64)) > 0)
+        assert np.array_equal(val[sl], cur[idx[sl]])
+        if int(flags.sum()) == int(got["n_anom"][u, a]):
+            assert np.array_equal(idx[sl], np.flatnonzero(flags))
+            checked += 1
+        i1, v1 = res.anomalies_unit(int(u))
+        assert np.array_equal(i1, idx[sl]) and np.array_equal(v1, val[sl])
+    assert checked >= min(10, np.count_nonzero(got["n_anom"][:, a])) * 0.8
+    assert int(got["first_idx"][np.flatnonzero(got["n_anom"][:, a])[0], a]) == int(idx[int(offsets[np.flatnonzero(got["n_anom"][:, a])[0]])])
+    res.free()
+    b.free()
+
+
 def test_device_csr_and_alignment_errors(ctx, oracle):
     import torch
     from foremast_b200._lib import ForemastGpuError
