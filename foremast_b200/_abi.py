@@ -10,8 +10,9 @@ import numpy as np
 ABI_VERSION = 1
 
 # error codes
-OK, E_INVALID, E_NOMEM, E_CUDA, E_NO_DEVICE, E_ALIGN, E_STATE, E_RANGE, E_UNSUPPORTED, E_COMM = (
-    0, -1, -2, -3, -4, -5, -6, -7, -8, -9)
+OK, E_INVALID, E_NOMEM, E_CUDA, E_NO_DEVICE, E_ALIGN, E_STATE, E_RANGE, E_UNSUPPORTED, E_COMM, E_TOO_LARGE = (
+    0, -1, -2, -3, -4, -5, -6, -7, -8, -9, -10)
+SCAN_STATIC_MAX_COUNTS = 16777216
 
 # ML_ALGORITHM bits (deploy/foremast/3_brain/foremast-brain.yaml:24-25, docs/guides/design.md:68-71)
 ALG_MA_ALL, ALG_MA_ROLLING, ALG_EWMA, ALG_DES, ALG_HW = 1, 2, 4, 8, 16

@@ -44,6 +44,7 @@ SYMBOLS = {
     "fm_result_anomalies_build": (C.c_int, [_P, C.c_uint32, C.POINTER(C.c_uint64)]),
     "fm_result_anomalies_unit": (C.c_int, [_P, C.c_uint64, _P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "fm_result_anomalies_all": (C.c_int, [_P, _P, _P, _P, C.c_uint64]),
+    "fm_scan_counts_static": (C.c_int, [_P, C.c_uint64, _P, _P]),
     "fm_result_service_buffers": (C.c_int, [_P, _PP, _PP, C.POINTER(C.c_uint32)]),
     "fm_result_timings": (C.c_int, [_P, C.POINTER(C.c_float), C.c_uint32]),
     "fm_result_free": (None, [_P]),

@@ -15,6 +15,16 @@ def default_params():
     return p
 
 
+def scan_counts_static(d_counts_ptr, n, d_offsets_ptr, stream=0):
+    """Allocation-free exclusive scan of per-unit anomaly counts (fm_scan_counts_static): device
+    uint32 counts[n] -> device uint64 offsets[n+1], on the current device and the given stream.
+    Raises ForemastGpuError(E_TOO_LARGE) beyond abi.SCAN_STATIC_MAX_COUNTS."""
+    L = load()
+    rc = L.fm_scan_counts_static(d_counts_ptr, n, d_offsets_ptr, stream)
+    if rc:
+        raise ForemastGpuError(rc, L.fm_strerror(rc).decode())
+
+
 class Context:
     def __init__(self, device=-1):
         self._L = load()

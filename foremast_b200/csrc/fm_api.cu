@@ -217,6 +217,7 @@ const char *fm_strerror(int code) {
     case FM_E_RANGE: return "index or size out of range";
     case FM_E_UNSUPPORTED: return "unsupported request";
     case FM_E_COMM: return "multi-GPU exchange failed";
+    case FM_E_TOO_LARGE: return "more items than this fixed-capacity entry point can take (see its limit in foremast_gpu.h)";
     default: return "unknown error";
   }
 }

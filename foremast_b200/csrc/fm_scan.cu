@@ -8,6 +8,8 @@
 // tile states (status in the top 2 bits of a 64-bit word, value below).  The tile states and the
 // ticket counter are SCRATCH: global memory that is neither input nor output and must start at
 // zero.  Algorithmic bytes: 4 in + 8 out per unit.
+#include <mutex>
+
 #include "fm_common.cuh"
 
 namespace {
@@ -106,4 +108,63 @@ cudaError_t fm_launch_scan_counts(const void *in, size_t stride, uint64_t n, uns
   if (e != cudaSuccess) return e;
   k_scan_counts<<<(unsigned)fm_scan_tiles(n), kThreads, 0, st>>>(static_cast<const unsigned char *>(in), stride, n, out, scratch);
   return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ allocation-free variant
+//
+// fm_scan_counts_static: the same exclusive scan for callers that are not allowed to allocate
+// device memory (see include/foremast_gpu.h).  Its tile states and ticket live in a fixed array
+// inside this module instead of a cudaMallocAsync'ed buffer, so the call is a memset plus a kernel
+// launch and nothing else.
+//
+// g_static_scratch is a __device__ symbol.  In host code that name is only a stand-in for the
+// symbol, NOT a device address -- handing it to a kernel would fault (or, where the GPU can reach
+// host memory, silently scribble on the wrong memory).  The address the kernel needs comes from
+// cudaGetSymbolAddress, asked once per device with that device current, and is kept in
+// g_static_ptr[device].
+namespace {
+
+constexpr uint64_t kStaticMaxCounts = FM_SCAN_STATIC_MAX_COUNTS;
+constexpr uint64_t kStaticMaxTiles = (kStaticMaxCounts + kTile - 1) / kTile;
+constexpr int kMaxDevices = 64;
+
+static __device__ __align__(256) unsigned long long g_static_scratch[kStaticMaxTiles + 1];  // 64 KiB + 8 B per GPU
+
+std::mutex g_static_mu;
+unsigned long long *g_static_ptr[kMaxDevices] = {nullptr};
+
+}  // namespace
+
+extern "C" int fm_scan_counts_static(const uint32_t *d_counts, uint64_t n, uint64_t *d_offsets, void *cuda_stream) {
+  if (!d_offsets || (n && !d_counts)) return FM_E_INVALID;
+  if (n > kStaticMaxCounts) return FM_E_TOO_LARGE;  // the fixed scratch cannot hold more tile states
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    cudaGetLastError();
+    return FM_E_NO_DEVICE;
+  }
+  unsigned long long *scratch;
+  {
+    std::lock_guard<std::mutex> g(g_static_mu);
+    if (!g_static_ptr[dev]) {  // first call on this device: resolve the symbol to a device address
+      void *p = nullptr;
+      if (cudaGetSymbolAddress(&p, g_static_scratch) != cudaSuccess || !p) {
+        cudaGetLastError();
+        return FM_E_CUDA;
+      }
+      g_static_ptr[dev] = static_cast<unsigned long long *>(p);
+    }
+    scratch = g_static_ptr[dev];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  // the array keeps whatever the previous call left in it: ticket and tile states must start at zero
+  if (cudaMemsetAsync(scratch, 0, fm_scan_scratch_bytes(n), st) != cudaSuccess) {
+    cudaGetLastError();
+    return FM_E_CUDA;
+  }
+  k_scan_counts<<<(unsigned)fm_scan_tiles(n), kThreads, 0, st>>>(reinterpret_cast<const unsigned char *>(d_counts),
+                                                               sizeof(uint32_t), n,
+                                                               reinterpret_cast<unsigned long long *>(d_offsets), scratch);
+  if (cudaGetLastError() != cudaSuccess) return FM_E_CUDA;
+  return FM_OK;
 }

@@ -40,7 +40,8 @@ enum {
   FM_E_STATE = -6,       /* call order violated (e.g. add after seal)                   */
   FM_E_RANGE = -7,       /* index / size outside what the call supports                 */
   FM_E_UNSUPPORTED = -8, /* valid request the build cannot serve                        */
-  FM_E_COMM = -9         /* multi-GPU exchange failed                                   */
+  FM_E_COMM = -9,        /* multi-GPU exchange failed                                   */
+  FM_E_TOO_LARGE = -10   /* more items than a fixed-capacity entry point can take       */
 };
 
 /* ---------------------------------------------------------------- vocabulary */
@@ -268,6 +269,33 @@ int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_poin
 int fm_result_anomalies_unit(fm_result *r, uint64_t unit, uint32_t *cur_idx, float *values, uint32_t cap, uint32_t *n);
 /* offsets has n_units+1 entries; cur_idx / values have room for cap >= n_points entries. */
 int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, float *values, uint64_t cap);
+/* fm_scan_counts_static -- NO COUNTERPART IN THE REFERENCE (the brain is a Python process that
+ * allocates freely); it exists for hosts that must not allocate GPU memory while they score.
+ *
+ * Who that is: a worker that sized its device arena once at start-up and runs under a fixed memory
+ * budget next to other tenants of the GPU; a scoring loop with a latency bound, where cudaMalloc /
+ * cudaFree may stall on the driver's allocator lock or synchronise the whole device; and code that
+ * is not allowed to fail for lack of memory half-way through a sweep.  Every other entry point of
+ * this library allocates result buffers; this one allocates nothing -- no cudaMalloc, cudaFree or
+ * stream-ordered pool call -- it clears a fixed scratch array that is part of the library image and
+ * launches one kernel.
+ *
+ * What it computes: the exclusive prefix sum that fm_result_anomalies_build uses to lay out the
+ * compact anomaly list.  d_counts[n] (device, uint32: anomalous points per unit) ->
+ * d_offsets[n+1] (device, uint64; d_offsets[n] = total).  Both buffers are the caller's.
+ *
+ * Limits and rules:
+ *  - n <= FM_SCAN_STATIC_MAX_COUNTS (16,777,216); more returns FM_E_TOO_LARGE and does nothing.
+ *    The scratch is 64 KiB of device memory per GPU that has loaded the library, held until exit.
+ *  - Runs on the CURRENT device, on `cuda_stream` (a cudaStream_t, NULL = default stream),
+ *    asynchronously: synchronise the stream before reading d_offsets.
+ *  - The first call on each device looks up the scratch array's device address
+ *    (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ *  - All calls on a device share the one scratch array: two calls whose GPU work can overlap
+ *    (different streams, or different threads) race and produce garbage.  Serialise them. */
+#define FM_SCAN_STATIC_MAX_COUNTS 16777216ull
+int fm_scan_counts_static(const uint32_t *d_counts, uint64_t n, uint64_t *d_offsets, void *cuda_stream);
+
 /* Device pointers of the dense per-service counters, for the cross-GPU merge:
  * counts = uint32[4*n_services] (n_units, n_unknown, n_anom_units, n_anom_points), summed;
  * worst  = uint64[n_services]   ((points << 32) | ~unit), maxed. */
