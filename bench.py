@@ -102,6 +102,15 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def host_threads():
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1; the oracle takes
+    the thread count explicitly)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_port_rate(oracle, csr, params, threads):
     t0 = time.perf_counter()
     oracle.score(csr, params, threads=threads)
@@ -116,7 +125,7 @@ def run_reference(args):
     if rank != 0:
         return
     from oracle import oracle
-    threads = oracle.max_threads()
+    threads = host_threads()
     sample = args.ref_units
     csr = oracle.synth(sample, N_HIST, N_BASE, N_CUR, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
                        flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
@@ -242,7 +251,7 @@ def run_ours(args):
                 traffic = None
         # CPU baseline: the oracle port on this box's host cores, bounded sample of the same workload
         from oracle import oracle
-        threads = oracle.max_threads()
+        threads = host_threads()
         sample = min(n, args.cpu_units)
         stride = int(host.offsets[1])
         sub = abi.HostCsr(host.values[:sample * stride + 32], host.offsets[:sample + 1], host.seg_lens[:sample],

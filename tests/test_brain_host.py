@@ -1,0 +1,71 @@
+"""Host-side logic of the job-level worker (foremast_b200/brain.py): the config-string format of
+foremast-service, the Prometheus matrix shape, the brain's environment block and the `reason` text
+that foremast-trigger parses.  CPU only; the GPU end-to-end job is in test_gpu_brain.py."""
+import html
+import json
+import re
+
+import numpy as np
+
+from foremast_b200 import _abi as abi
+from foremast_b200 import brain
+from oracle import oracle
+
+
+def test_parse_config_roundtrip_of_service_format():
+    # what convertMetricQuerys emits (foremast-service/cmd/manager/main.go:50-81)
+    urls = {"error5xx": "http://prom:9090/api/v1/query_range?query=namespace_pod_http_errors_5xx%7Bpod%3D~%22a%7Cb%22%7D&start=START_TIME&end=END_TIME&step=60",
+            "latency": "http://prom:9090/api/v1/query_range?query=lat&start=100&end=700&step=60"}
+    cfg = brain.CONFIG_SEPARATOR.join(k + brain.KV_SEPARATOR + v for k, v in urls.items())
+    assert " ||" in cfg and "== " in cfg
+    got = brain.parse_config(cfg)
+    assert got == urls
+    u = brain.substitute_times(got["error5xx"], 1550000000, 1550001800.9)
+    assert "start=1550000000&end=1550001800&step=60" in u
+    assert brain.query_window(got["latency"]) == (100.0, 700.0, 60.0)
+    assert brain.parse_config("") == {}
+
+
+def test_parse_matrix_and_units():
+    payload = {"status": "success", "data": {"resultType": "matrix", "result": [
+        {"metric": {"pod": "a"}, "values": [[1000, "0.5"], [1060, "NaN"], [1120, "2"]]},
+        {"metric": {"pod": "b"}, "values": [[1000, "1.5"]]}]}}
+    m = brain.parse_matrix(json.dumps(payload))
+    assert len(m) == 2 and m[0][1] == 1000.0 and m[0][2].dtype == np.float32
+    assert np.isnan(m[0][2][1]) and m[0][2][2] == 2.0
+    units, meta = brain.build_units({"cpu": [({}, 0.0, np.ones(5, np.float32))]}, {"cpu": m[:1]}, {"cpu": m})
+    assert len(units) == 2 and meta[1]["labels"] == {"pod": "b"} and meta[0]["metric_type"] == abi.MT_CPU
+    assert units[1][1] is units[0][1]  # fewer baseline series than current: the last one is reused
+    assert [brain.metric_type_of(a) for a in ("error5xx", "http_4xx", "p99_latency", "cpu", "memory_used", "tps", "weird")] == \
+        [abi.MT_ERROR5XX, abi.MT_ERROR4XX, abi.MT_LATENCY, abi.MT_CPU, abi.MT_MEMORY, abi.MT_TPS, abi.MT_OTHER]
+
+
+def test_params_from_brain_yaml_env():
+    """The literal env block of deploy/foremast/3_brain/foremast-brain.yaml:21-81 reproduces the defaults."""
+    env = {"ML_ALGORITHM": "moving_average_all", "threshold": "2.0", "min_lower_bound": "0", "bound": "1",
+           "metric_type_threshold_count": "5",
+           "metric_type0": "error5xx", "threshold0": "2", "bound0": "1", "min_lower_bound0": "0",
+           "metric_type1": "error4xx", "threshold1": "3", "bound1": "1", "min_lower_bound1": "0",
+           "metric_type2": "latency", "threshold2": "10", "bound2": "3", "min_lower_bound2": "0",
+           "metric_type3": "cpu", "threshold3": "5", "bound3": "1", "min_lower_bound3": "0",
+           "metric_type4": "memory", "threshold4": "5", "bound4": "1", "min_lower_bound4": "0",
+           "MIN_MANN_WHITE_DATA_POINTS": "20", "MIN_WILCOXON_DATA_POINTS": "20", "MIN_KRUSKAL_DATA_POINTS": "5"}
+    blank = abi.Params()
+    blank.rules[0].bound = 1
+    p = brain.params_from_env(env, oracle.params_default())
+    assert bytes(p) == bytes(oracle.params_default())
+    q = brain.params_from_env({"ML_ALGORITHM": "holt_winters exponential_smoothing", "ML_PAIRWISE_ALGORITHM": "ANY",
+                               "ML_PAIRWISE_THRESHOLD": "0.01"}, oracle.params_default())
+    assert q.algorithms == abi.ALG_HW | abi.ALG_EWMA and q.pairwise == abi.PW_ANY and q.pairwise_threshold == 0.01
+
+
+def test_reason_text_matches_trigger_regexes():
+    pairs = brain.anomaly_pairs(1550000000.0, 60, [1, 21], [40.134, 40.466])
+    assert pairs == [1550000060.0, 40.134, 1550001260.0, 40.466]
+    r = brain.reason_text([{"alias": "error5xx", "tags": "{}", "pairs": pairs}])
+    # foremast-trigger/pkg/foremasttrigger/trigger.go:295,309
+    m = re.search(r"&quot;name&quot;\s*:\s*&quot;([\w\.]*)", r)
+    assert m and m.group(1) == "error5xx"
+    t = re.search(r"&quot;ts&quot;\s*:\s*\[(\d*).\d", r)
+    assert t and t.group(1) == "1550000060"
+    assert json.loads(html.unescape(r))["anomaly"][0]["values"] == [40.134, 40.466]  # trigger.go:363 un-escapes
