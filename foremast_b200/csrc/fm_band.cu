@@ -10,7 +10,7 @@
 // bands and therefore flags are bit-identical to the CPU oracle; the parallelism comes from the
 // 10^5..10^7 independent series, not from scanning inside one.  HBM access stays coalesced by
 // staging: each warp pulls, per stage, a 128 B row (32 samples) of each of its 32 units with
-// 16 B cp.async copies (every 128 B line fully used by one instruction) into a 3-deep shared
+// 16 B cp.async copies (every 128 B line fully used by one instruction) into a 2-deep shared
 // memory ring, and each lane then walks its own row with conflict-free 128-bit LDS (row stride
 // 36 words).  Algorithmic bytes per unit: 4*(n_hist+n_base+n_cur) + 8 (offset) + 12 (lengths)
 // + results.
@@ -20,8 +20,8 @@ namespace {
 
 constexpr int kChunk = 32;        // samples per row per stage
 constexpr int kRowWords = 36;     // 32 + 4 pad words: 16 B aligned rows, conflict-free LDS.128
-constexpr int kStages = 3;
-constexpr int kWarpsPerBlock = 4;
+constexpr int kStages = 2;        // current chunk + one in flight (deeper rings cost occupancy: 3 -> 2 gained 12 %)
+constexpr int kWarpsPerBlock = 8;
 constexpr int kRingBytes = kWarpsPerBlock * kStages * 32 * kRowWords * 4;
 constexpr int kSmemBytes = kRingBytes + kWarpsPerBlock * 32 * (8 + 4);
 
@@ -29,6 +29,9 @@ struct Rule {
   double k, mlb;
   uint32_t bound;
 };
+
+template <int N>
+struct IntC { static constexpr int value = N; };
 
 template <uint32_t ALGS>
 struct State {
@@ -111,6 +114,53 @@ __device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t
   }
   if (ALGS & FM_ALG_EWMA) s.esig = ns >= 2 ? sqrt(s.esse / (double)(ns - 1)) : 0.0;
   if (ALGS & FM_ALG_DES) s.dsig = ns >= 2 ? sqrt(s.dsse / (double)(ns - 1)) : 0.0;
+}
+
+// Per-thread form of the rule for the fast path: x < max(mlb, lo) is evaluated as
+// (x < lo) || (x < mlb), which needs no fp64 max, and a disabled side is a constant-false predicate.
+struct FastRule {
+  double k, nk, mlb;
+  bool up_on, lo_on;
+};
+
+__device__ __forceinline__ bool outside_fast(double x, double up, double lo, const FastRule &fr) {
+  return (fr.up_on && x > up) || (fr.lo_on && (x < lo || x < fr.mlb));
+}
+
+// Fast-path twin of cur_update for chunks that lie entirely inside the current window: identical
+// arithmetic, but flags are gathered into one bit mask per algorithm per 32-sample chunk (bit I)
+// and counted once per chunk instead of being counted point by point.
+template <uint32_t ALGS, int I>
+__device__ __forceinline__ void cur_fast(State<ALGS> &s, const FastRule &fr, double xd, uint32_t j, bool valid,
+                                         double alpha, double ab, uint32_t (&mask)[4], const Lag &lag) {
+  if (ALGS & FM_ALG_MA_ROLLING) {
+    const uint32_t q = lag.ns + j, cnt = lag.W < q ? lag.W : q;
+    const double a1 = s.rp1 - s.rq1, a2 = s.rp2 - s.rq2;
+    const double m1 = a1 / (double)cnt, mean = s.x0 + m1;
+    double var = fma(-m1, m1, a2 / (double)cnt);
+    if (!(var > 0.0)) var = 0.0;
+    const double sd = sqrt(var), up = fma(fr.k, sd, mean), lo = fma(fr.nk, sd, mean);
+    if (valid) s.rsd = sd;
+    if (outside_fast(xd, up, lo, fr)) mask[3] |= 1u << I;
+    roll_advance<ALGS>(s, xd, q, lag, valid);
+  }
+  if (ALGS & FM_ALG_MA_ALL) {
+    // s.ma_lo already carries the clamp, so the plain comparison is the oracle's
+    if ((fr.up_on && xd > s.ma_up) || (fr.lo_on && xd < s.ma_lo)) mask[0] |= 1u << I;
+  }
+  if (ALGS & FM_ALG_EWMA) {
+    const double f0 = s.es, up = fma(fr.k, s.esig, f0), lo = fma(fr.nk, s.esig, f0);
+    if (outside_fast(xd, up, lo, fr)) mask[1] |= 1u << I;
+    const double e = xd - f0;
+    s.es = fma(alpha, e, s.es);
+  }
+  if (ALGS & FM_ALG_DES) {
+    const double f0 = s.dl + s.db, up = fma(fr.k, s.dsig, f0), lo = fma(fr.nk, s.dsig, f0);
+    if (outside_fast(xd, up, lo, fr)) mask[2] |= 1u << I;
+    const double e = xd - f0;
+    s.dl = fma(alpha, e, f0);
+    s.db = fma(ab, e, s.db);
+  }
 }
 
 // One current point: flag against each band, then keep the smoothers running (D4).
@@ -214,6 +264,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     r.mlb = dr.min_lower_bound;
     r.bound = dr.bound;
   }
+  FastRule fr;
+  fr.k = r.k; fr.nk = -r.k; fr.mlb = r.mlb;
+  fr.up_on = (r.bound & 1u) != 0; fr.lo_on = (r.bound & 2u) != 0;
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta;
   const uint32_t band_alg = BANDS ? dp->band_algorithm : 0u;
 
@@ -279,15 +332,25 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
         src_update<ALGS>(s, (double)x.w, alpha, ab, q + 3, lag, cls_src);
       }
     } else if (MODE == 0 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
-      float du, dl;
-#pragma unroll
-      for (int v4 = 0; v4 < 8; ++v4) {
+      uint32_t mask[4] = {0u, 0u, 0u, 0u};
+      const uint32_t j0 = cs - c0;
+      auto quad = [&](auto V4) {
+        constexpr int v4 = decltype(V4)::value;
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
-        const uint32_t j = cs + v4 * 4 - c0;
-        cur_update<ALGS>(s, r, (double)x.x, j + 0, cls_cur, alpha, ab, du, dl, 0u, lag);
-        cur_update<ALGS>(s, r, (double)x.y, j + 1, cls_cur, alpha, ab, du, dl, 0u, lag);
-        cur_update<ALGS>(s, r, (double)x.z, j + 2, cls_cur, alpha, ab, du, dl, 0u, lag);
-        cur_update<ALGS>(s, r, (double)x.w, j + 3, cls_cur, alpha, ab, du, dl, 0u, lag);
+        cur_fast<ALGS, v4 * 4 + 0>(s, fr, (double)x.x, j0 + v4 * 4 + 0, cls_cur, alpha, ab, mask, lag);
+        cur_fast<ALGS, v4 * 4 + 1>(s, fr, (double)x.y, j0 + v4 * 4 + 1, cls_cur, alpha, ab, mask, lag);
+        cur_fast<ALGS, v4 * 4 + 2>(s, fr, (double)x.z, j0 + v4 * 4 + 2, cls_cur, alpha, ab, mask, lag);
+        cur_fast<ALGS, v4 * 4 + 3>(s, fr, (double)x.w, j0 + v4 * 4 + 3, cls_cur, alpha, ab, mask, lag);
+      };
+      quad(IntC<0>{}); quad(IntC<1>{}); quad(IntC<2>{}); quad(IntC<3>{});
+      quad(IntC<4>{}); quad(IntC<5>{}); quad(IntC<6>{}); quad(IntC<7>{});
+      if (cls_cur) {  // lanes that only ride along (done / not started) keep their counters
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+          if (mask[a]) {
+            if (s.cnt[a] == 0) s.first[a] = j0 + (uint32_t)(__ffs(mask[a]) - 1);
+            s.cnt[a] += __popc(mask[a]);
+          }
       }
     } else if (!__all_sync(0xffffffffu, cls_skip)) {
       // generic path: chunk straddles a segment edge for at least one lane
