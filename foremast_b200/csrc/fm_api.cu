@@ -627,7 +627,7 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
 
   const DevBatch db = dev_view(b);
   FM_R(cudaEventRecord(r->ev[1], st));
-  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, std::max(b->max_base, b->max_cur), r->d_scores, ctx->sm_count, st));
+  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), r->d_scores, ctx->sm_count, st));
   FM_R(cudaEventRecord(r->ev[2], st));
   const bool band_in_kband = (p->band_algorithm & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES)) != 0;
   FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, r->d_scores, r->d_unit_status, r->d_unit_points,

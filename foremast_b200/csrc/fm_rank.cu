@@ -11,9 +11,10 @@
 // inside a lane are two FMNMX/VIMNMX, the 15 lane-crossing stages use SHFL.BFLY -- so the sort
 // never touches memory.  Baseline and current are sorted separately and payload-free (group
 // membership is recovered by merging, not carried through the sort); Wilcoxon sorts one u32 key
-// per pair with the sign in bit 0.  The sorted runs go to a padded shared-memory tile and the 32
-// lanes split the merged order by merge path (fm_rank_merge.h) to accumulate exact int64 rank
-// sums and tie terms.  Reads are plain coalesced 4-byte loads: segment starts are not 16 B
+// per pair with the sign in bit 0.  Tie runs are measured while the sorted keys are still in
+// registers (run_pass); the sorted runs then go to padded shared-memory tiles and the 32 lanes
+// split the merged order by merge path (fm_rank_merge.h), each walking an equal span with a
+// uniform trip count, to accumulate exact int64 rank sums and tie terms.  Reads are plain coalesced 4-byte loads: segment starts are not 16 B
 // aligned in general, and this kernel is issue-bound on the sort, not on HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
 #include "fm_common.cuh"
@@ -95,6 +96,74 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsign
   }
 }
 
+// Tie bookkeeping of one sorted run stored in a shared-memory tile (element e at fm_pidx(e), the
+// lane owns elements lane*R .. lane*R+R-1, the first n are real).  Equal keys (after dropping the
+// low `sh` bits) form runs; for each run [s, s+t) the lane that holds its LAST element adds
+// t^3 - t to `ties`, stores t at rl[s] (if rl is given) and, for Wilcoxon keys (sign in bit 0,
+// positives first inside a run), adds cpos * (2s + t + 1) to `acc2` -- cpos positives at
+// twice-average-rank 2s + t + 1.  Two sweeps and two warp scans (run start / prefix count of
+// positives carried across lanes), uniform trip counts.  Only units that HAVE ties come here, so
+// it is a compact out-of-line routine (rolled loops over shared memory) rather than unrolled
+// register code: the kernel's instruction footprint is what limits its issue rate.
+__device__ __noinline__ void run_pass(const uint32_t *tile, const int R, const uint32_t sh, const bool wilcoxon,
+                                      const unsigned lane, const uint32_t n, uint16_t *rl, long long *ties_out,
+                                      long long *acc2_out) {
+  const uint32_t base = lane * R;
+  const uint32_t prevk = base ? tile[fm_pidx(base - 1)] : 0u;
+  // sweep 1: last run start inside this lane, positives before it, positives in the lane
+  int last_head = -1;
+  uint32_t ps_last = 0, pos_cnt = 0, gp = prevk >> sh;
+  for (int r = 0; r < R; ++r) {
+    const uint32_t e = base + r, k = tile[fm_pidx(e)], g = k >> sh;
+    if (e < n && (e == 0 || g != gp)) { last_head = (int)e; ps_last = pos_cnt; }
+    if (wilcoxon && e < n && !(k & 1u)) ++pos_cnt;
+    gp = g;
+  }
+  uint32_t pbase = pos_cnt;  // exclusive prefix sum of positives over lanes
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, pbase, o);
+    if ((int)lane >= o) pbase += t;
+  }
+  pbase -= pos_cnt;
+  // run start (and positives before it) carried in from the nearest earlier lane that has one
+  int s_in = last_head;
+  uint32_t ps_in = pbase + ps_last;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int s2 = __shfl_up_sync(0xffffffffu, s_in, o);
+    const uint32_t p2 = __shfl_up_sync(0xffffffffu, ps_in, o);
+    if ((int)lane >= o && s2 > s_in) { s_in = s2; ps_in = p2; }
+  }
+  s_in = __shfl_up_sync(0xffffffffu, s_in, 1);
+  ps_in = __shfl_up_sync(0xffffffffu, ps_in, 1);
+  if (lane == 0) { s_in = -1; ps_in = 0; }
+  // sweep 2: close runs at their last element
+  int s_cur = s_in;
+  uint32_t ps_cur = ps_in, cnt = pbase;
+  long long ties = 0, acc2 = 0;
+  gp = prevk >> sh;
+  uint32_t k = tile[fm_pidx(base)];
+  for (int r = 0; r < R; ++r) {
+    const uint32_t e = base + r, g = k >> sh;
+    const uint32_t kn = tile[fm_pidx(e + 1)];  // the slot after the run holds the sentinel
+    if (e < n) {
+      if (e == 0 || g != gp) { s_cur = (int)e; ps_cur = cnt; }
+      if (wilcoxon && !(k & 1u)) ++cnt;
+      if (e + 1 == n || g != (kn >> sh)) {
+        const long long t = (long long)e + 1 - s_cur;
+        if (rl) rl[s_cur] = (uint16_t)t;
+        if (wilcoxon) acc2 += (long long)(cnt - ps_cur) * (2ll * s_cur + t + 1);
+        if (t > 1) ties += t * t * t - t;
+      }
+    }
+    gp = g;
+    k = kn;
+  }
+  *ties_out = ties;
+  *acc2_out = acc2;
+}
+
 // p-values: same expressions, same order as oracle/DECISIONS.md "p-values".
 __device__ __noinline__ double p_mann_whitney(long long u1x2, uint32_t n1, uint32_t n2, long long ties) {
   double nn = (double)n1 * (double)n2, N = (double)n1 + (double)n2;
@@ -132,11 +201,17 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
   return p > 1.0 ? 1.0 : p;
 }
 
-template <int R>
+// PHASE 0: Wilcoxon signed-rank (one sort of |d| keys).  PHASE 1: Mann-Whitney / Kruskal-Wallis
+// (baseline and current sorted separately, merge-path walk).  Two launches instead of one fused
+// kernel: each keeps its instruction footprint inside the instruction cache (the fused kernel
+// lost 4-5 issue slots per issued instruction to fetch stalls), and both are ALU-bound, so the
+// second read of the samples (from L2/HBM) costs nothing measurable.
+template <int R, int PHASE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, const DevParams *__restrict__ dp,
                                                               fm_series_score *__restrict__ scores) {
-  constexpr int kTile = 33 * R + 2;  // padded words per sorted run (+ one sentinel slot)
-  extern __shared__ uint32_t s_tiles[];  // [warps][2][kTile]: baseline keys, current keys (|d| keys borrow the 2nd)
+  constexpr int kTile = 33 * R + 2;   // padded words per sorted run (+ one sentinel slot)
+  constexpr int kRl = 32 * R + 2;     // run-length table per sorted run (u16)
+  extern __shared__ uint32_t s_tiles[];  // [warps][2][kTile] keys, then [warps][2][kRl] u16 run lengths
 
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t pairwise = dp->pairwise;
@@ -144,6 +219,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
   const bool want_k = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_KRUSKAL;
   uint32_t *const sA = s_tiles + (size_t)warp * 2 * kTile, *const sB = sA + kTile;
+  uint16_t *const rlA = reinterpret_cast<uint16_t *>(s_tiles + (size_t)kWarpsPerBlock * 2 * kTile) + (size_t)warp * 2 * kRl;
+  uint16_t *const rlB = rlA + kRl;
 
   // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
   const uint64_t n_rounds = (b.n_units + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
@@ -169,22 +246,22 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
     const float *base = b.values + off + nh, *cur = base + nb;
     const uint32_t m = min(nb, nc);
     const bool fits = nb <= 32u * R && nc <= 32u * R;
-    const bool run_mw = have && want_mw && nb >= dp->min_mann_white && nc >= dp->min_mann_white && m > 0 && fits;
-    const bool run_w = have && want_w && m >= dp->min_wilcoxon && m > 0 && fits;
-    const bool run_k = have && want_k && nb >= dp->min_kruskal && nc >= dp->min_kruskal && m > 0 && fits;
+    const bool run_mw = PHASE == 1 && have && want_mw && nb >= dp->min_mann_white && nc >= dp->min_mann_white && m > 0 && fits;
+    const bool run_w = PHASE == 0 && have && want_w && m >= dp->min_wilcoxon && m > 0 && fits;
+    const bool run_k = PHASE == 1 && have && want_k && nb >= dp->min_kruskal && nc >= dp->min_kruskal && m > 0 && fits;
     const bool pooled = run_mw || run_k;
 
     long long w_2wp = 0, w_ties = 0, mw_2r1 = 0, mw_ties = 0;
     uint32_t w_n = 0;
-    bool ties_within = false;  // equal samples inside the baseline or inside the current segment
+    bool tie_a = false, tie_b = false;  // equal samples inside the baseline / inside the current segment
 
     // one sort routine, three passes: |d| keys (Wilcoxon), baseline, current
 #pragma unroll 1
-    for (int seg = 0; seg < 3; ++seg) {
+    for (int seg = PHASE == 0 ? 0 : 1; seg < (PHASE == 0 ? 1 : 3); ++seg) {
       if (seg == 0 ? !run_w : !pooled) continue;
       uint32_t key[R];
       uint32_t n_valid;
-      if (seg == 0) {
+      if (PHASE == 0) {
         uint32_t nz = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -212,7 +289,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
       warp_bitonic_sort<R>(key, lane);
 
       // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1)
-      const uint32_t sh = seg == 0 ? 1u : 0u;  // |d| keys carry the sign in bit 0
+      const uint32_t sh = PHASE == 0 ? 1u : 0u;  // |d| keys carry the sign in bit 0
       bool tie = false;
 #pragma unroll
       for (int r = 0; r + 1 < R; ++r)
@@ -221,61 +298,68 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
       tie = tie || (lane < 31 && ((key[R - 1] >> sh) == (nxt >> sh)) && (lane * R + R < n_valid));
       const bool any_tie = __any_sync(0xffffffffu, tie);
 
-      if (seg == 0 && !any_tie) {
-        // tie-free |d|: the rank of sorted position e is e+1, no shared memory needed
-        int acc = 0;
+      if (PHASE == 0) {
+        long long acc = 0, tt = 0;
+        if (!any_tie) {
+          // tie-free |d|: the rank of sorted position e is e+1
+          int a32 = 0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const uint32_t e = lane * R + r;
-          if (e < n_valid && !(key[r] & 1u)) acc += 2 * (int)(e + 1);
+          for (int r = 0; r < R; ++r) {
+            const uint32_t e = lane * R + r;
+            if (e < n_valid && !(key[r] & 1u)) a32 += 2 * (int)(e + 1);
+          }
+          acc = a32;
+        } else {
+#pragma unroll
+          for (int r = 0; r < R; ++r) sB[fm_pidx(lane * R + r)] = key[r];
+          if (lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
+          __syncwarp();
+          run_pass(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
+          __syncwarp();
         }
-        w_2wp = __reduce_add_sync(0xffffffffu, (uint32_t)acc);
+        w_2wp = warp_sum_i64(acc);
+        w_ties = any_tie ? warp_sum_i64(tt) : 0;
       } else {
         uint32_t *dst = seg == 1 ? sA : sB;
 #pragma unroll
         for (int r = 0; r < R; ++r) dst[fm_pidx(lane * R + r)] = key[r];
         if (lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
-        if (seg == 0) {
+        if (any_tie) {
+          long long tt = 0, unused = 0;
           __syncwarp();
-          fm_w_lane(sB, (int)w_n, (int)lane, w_2wp, w_ties);
-          w_2wp = warp_sum_i64(w_2wp);
-          w_ties = warp_sum_i64(w_ties);
-          __syncwarp();
-        } else {
-          ties_within = ties_within || any_tie;
+          run_pass(dst, R, 0u, false, lane, n_valid, seg == 1 ? rlA : rlB, &tt, &unused);
+          mw_ties += tt;  // per-lane partial of T_A + T_B, reduced below
+          if (seg == 1) tie_a = true; else tie_b = true;
         }
       }
     }
     if (pooled) {
       __syncwarp();
-      bool slow = ties_within;
-      if (!slow) {
-        int plt;
-        const bool cross = fm_mw_lane_fast(sA, (int)nb, sB, (int)nc, (int)lane, plt);
-        slow = __any_sync(0xffffffffu, cross);
-        if (!slow) mw_2r1 = (long long)nb * ((long long)nb + 1) + 2ll * (long long)__reduce_add_sync(0xffffffffu, (uint32_t)plt);
-      }
-      if (slow) {
-        fm_mw_lane(sA, (int)nb, sB, (int)nc, (int)lane, mw_2r1, mw_ties);
-        mw_2r1 = warp_sum_i64(mw_2r1);
-        mw_ties = warp_sum_i64(mw_ties);
-      }
+      int plt;
+      long long peq, x3;
+      fm_mw_walk(sA, (int)nb, sB, (int)nc, tie_a ? rlA : nullptr, tie_b ? rlB : nullptr, (int)lane, plt, peq, x3);
+      const long long plt_sum = warp_sum_i64((long long)plt), peq_sum = warp_sum_i64(peq);
+      mw_2r1 = (long long)nb * ((long long)nb + 1) + 2 * plt_sum + peq_sum;
+      mw_ties = warp_sum_i64(mw_ties + 3 * x3);
       __syncwarp();
     }
 
     // ---- exact integer statistics out; p-values and the combiner run one thread per unit in
-    //      k_rank_finalize (three lanes of a warp doing erfc here cost a third of the kernel's
-    //      instruction footprint for 3/32 of its lanes)
+    //      k_rank_finalize
     if (lane == 0 && have) {
       fm_series_score *o = scores + u;
-      o->status = (run_mw ? FM_S_MW_RUN : 0u) | (run_w ? FM_S_WILCOXON_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u);
-      o->w_n = w_n;
-      o->mw_2u1 = pooled ? mw_2r1 - (long long)nb * ((long long)nb + 1) : 0;
-      o->mw_2r1 = pooled ? mw_2r1 : 0;
-      o->mw_ties = pooled ? mw_ties : 0;
-      o->w_2wplus = w_2wp;
-      o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
-      o->w_ties = w_ties;
+      if (PHASE == 0) {
+        o->status = run_w ? FM_S_WILCOXON_RUN : 0u;  // first writer (scores start zeroed)
+        o->w_n = w_n;
+        o->w_2wplus = w_2wp;
+        o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
+        o->w_ties = w_ties;
+      } else {
+        o->status |= (run_mw ? FM_S_MW_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u);
+        o->mw_2u1 = pooled ? mw_2r1 - (long long)nb * ((long long)nb + 1) : 0;
+        o->mw_2r1 = pooled ? mw_2r1 : 0;
+        o->mw_ties = pooled ? mw_ties : 0;
+      }
     }
   }
 }
@@ -308,17 +392,21 @@ __global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevPara
 }
 
 template <int R>
-cudaError_t launch(const DevBatch &b, const DevParams *dp, fm_series_score *scores, int sm_count, cudaStream_t st) {
+cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool want_pooled, fm_series_score *scores,
+                   int sm_count, cudaStream_t st) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
     // many more blocks than are resident: tie-heavy units take longer, the block scheduler evens it
   // out (a persistent 5-blocks-per-SM grid measured 19 % slower)
   const uint64_t cap = (uint64_t)sm_count * 64;
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  constexpr int smem = kWarpsPerBlock * 2 * (33 * R + 2) * 4;
-  cudaError_t e = cudaFuncSetAttribute(k_rank<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  constexpr int smem = kWarpsPerBlock * 2 * ((33 * R + 2) * 4 + (32 * R + 2) * 2);
+  cudaError_t e = cudaFuncSetAttribute(k_rank<R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  k_rank<R><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
+  e = cudaFuncSetAttribute(k_rank<R, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
+  if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
   k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
   return cudaGetLastError();
 }
@@ -327,13 +415,16 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, fm_series_score *scor
 
 // max_seg = longest baseline / current segment in the batch; segments above 1024 samples are
 // not ranked by this kernel (the caller reports FM_E_UNSUPPORTED).
-cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t max_seg, fm_series_score *scores,
-                           int sm_count, cudaStream_t st) {
-  if (max_seg <= 32) return launch<1>(b, dp, scores, sm_count, st);
-  if (max_seg <= 64) return launch<2>(b, dp, scores, sm_count, st);
-  if (max_seg <= 128) return launch<4>(b, dp, scores, sm_count, st);
-  if (max_seg <= 256) return launch<8>(b, dp, scores, sm_count, st);
-  if (max_seg <= 512) return launch<16>(b, dp, scores, sm_count, st);
-  if (max_seg <= 1024) return launch<32>(b, dp, scores, sm_count, st);
+cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_seg,
+                           fm_series_score *scores, int sm_count, cudaStream_t st) {
+  const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
+  const bool w = all || pairwise == FM_PW_WILCOXON;
+  const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
+  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, scores, sm_count, st);
   return cudaErrorInvalidValue;
 }
