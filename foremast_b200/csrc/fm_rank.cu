@@ -17,6 +17,8 @@
 // uniform trip count, to accumulate exact int64 rank sums and tie terms.  Reads are plain coalesced 4-byte loads: segment starts are not 16 B
 // aligned in general, and this kernel is issue-bound on the sort, not on HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
+#include <algorithm>
+
 #include "fm_common.cuh"
 #include "fm_rank_merge.h"
 
@@ -109,12 +111,12 @@ __device__ __noinline__ void run_pass(const uint32_t *tile, const int R, const u
                                       const unsigned lane, const uint32_t n, uint16_t *rl, long long *ties_out,
                                       long long *acc2_out) {
   const uint32_t base = lane * R;
-  const uint32_t prevk = base ? tile[fm_pidx(base - 1)] : 0u;
+  const uint32_t prevk = (base && base - 1 <= n) ? tile[fm_pidx(base - 1)] : 0xFFFFFFFFu;
   // sweep 1: last run start inside this lane, positives before it, positives in the lane
   int last_head = -1;
   uint32_t ps_last = 0, pos_cnt = 0, gp = prevk >> sh;
   for (int r = 0; r < R; ++r) {
-    const uint32_t e = base + r, k = tile[fm_pidx(e)], g = k >> sh;
+    const uint32_t e = base + r, k = e <= n ? tile[fm_pidx(e)] : 0xFFFFFFFFu, g = k >> sh;
     if (e < n && (e == 0 || g != gp)) { last_head = (int)e; ps_last = pos_cnt; }
     if (wilcoxon && e < n && !(k & 1u)) ++pos_cnt;
     gp = g;
@@ -143,10 +145,10 @@ __device__ __noinline__ void run_pass(const uint32_t *tile, const int R, const u
   uint32_t ps_cur = ps_in, cnt = pbase;
   long long ties = 0, acc2 = 0;
   gp = prevk >> sh;
-  uint32_t k = tile[fm_pidx(base)];
+  uint32_t k = base <= n ? tile[fm_pidx(base)] : 0xFFFFFFFFu;
   for (int r = 0; r < R; ++r) {
     const uint32_t e = base + r, g = k >> sh;
-    const uint32_t kn = tile[fm_pidx(e + 1)];  // the slot after the run holds the sentinel
+    const uint32_t kn = e + 1 <= n ? tile[fm_pidx(e + 1)] : 0xFFFFFFFFu;  // slot n holds the sentinel
     if (e < n) {
       if (e == 0 || g != gp) { s_cur = (int)e; ps_cur = cnt; }
       if (wilcoxon && !(k & 1u)) ++cnt;
@@ -207,10 +209,14 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
 // lost 4-5 issue slots per issued instruction to fetch stalls), and both are ALU-bound, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
 template <int R, int PHASE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, const DevParams *__restrict__ dp,
-                                                              fm_series_score *__restrict__ scores) {
-  constexpr int kTile = 33 * R + 2;   // padded words per sorted run (+ one sentinel slot)
-  constexpr int kRl = 32 * R + 2;     // run-length table per sorted run (u16)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) k_rank(DevBatch b, const DevParams *__restrict__ dp,
+                                                              fm_series_score *__restrict__ scores, const int tile_words,
+                                                              const int kRl) {
+  // PHASE 0 keeps the compile-time tile (one tile per warp is small anyway; a run-time size cost it
+  // registers and 18 % of its speed); PHASE 1 sizes its four tables for the batch
+  const int kTile = PHASE == 0 ? 33 * R + 2 : tile_words;
+  // kTile: padded words per sorted run (+ sentinel slot), kRl: run-length entries (u16) per run; both
+  // sized by the host for the longest segment of the batch, not for the 32*R capacity of the sort
   extern __shared__ uint32_t s_tiles[];  // [warps][2][kTile] keys, then [warps][2][kRl] u16 run lengths
 
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
@@ -218,8 +224,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
   const bool want_mw = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_MANN_WHITE;
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
   const bool want_k = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_KRUSKAL;
-  uint32_t *const sA = s_tiles + (size_t)warp * 2 * kTile, *const sB = sA + kTile;
-  uint16_t *const rlA = reinterpret_cast<uint16_t *>(s_tiles + (size_t)kWarpsPerBlock * 2 * kTile) + (size_t)warp * 2 * kRl;
+  // PHASE 0 only ever needs one tile (the tie pass of the |d| keys): a smaller footprint, more warps
+  constexpr int kTilesPerWarp = PHASE == 0 ? 1 : 2;
+  uint32_t *const sA = s_tiles + (size_t)warp * kTilesPerWarp * kTile, *const sB = PHASE == 0 ? sA : sA + kTile;
+  uint16_t *const rlA = reinterpret_cast<uint16_t *>(s_tiles + (size_t)kWarpsPerBlock * kTilesPerWarp * kTile) + (size_t)warp * 2 * kRl;
   uint16_t *const rlB = rlA + kRl;
 
   // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
@@ -311,8 +319,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
           acc = a32;
         } else {
 #pragma unroll
-          for (int r = 0; r < R; ++r) sB[fm_pidx(lane * R + r)] = key[r];
-          if (lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
+          for (int r = 0; r < R; ++r)
+            if (lane * R + r <= n_valid) sB[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+          if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
           __syncwarp();
           run_pass(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
           __syncwarp();
@@ -322,8 +331,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 5) k_rank(DevBatch b, con
       } else {
         uint32_t *dst = seg == 1 ? sA : sB;
 #pragma unroll
-        for (int r = 0; r < R; ++r) dst[fm_pidx(lane * R + r)] = key[r];
-        if (lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
+        for (int r = 0; r < R; ++r)
+          if (lane * R + r <= n_valid) dst[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+        if (n_valid == 32u * R && lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
         if (any_tie) {
           long long tt = 0, unused = 0;
           __syncwarp();
@@ -392,21 +402,24 @@ __global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevPara
 }
 
 template <int R>
-cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool want_pooled, fm_series_score *scores,
-                   int sm_count, cudaStream_t st) {
+cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool want_pooled, uint32_t max_seg,
+                   fm_series_score *scores, int sm_count, cudaStream_t st) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
     // many more blocks than are resident: tie-heavy units take longer, the block scheduler evens it
   // out (a persistent 5-blocks-per-SM grid measured 19 % slower)
   const uint64_t cap = (uint64_t)sm_count * 64;
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  constexpr int smem = kWarpsPerBlock * 2 * ((33 * R + 2) * 4 + (32 * R + 2) * 2);
-  cudaError_t e = cudaFuncSetAttribute(k_rank<R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
+  const int tile_words = seg_cap + (seg_cap >> 5) + 2, rl_entries = (seg_cap + 2 + 1) & ~1;
+  const int smem = kWarpsPerBlock * 2 * (tile_words * 4 + rl_entries * 2);
+  const int smem_w = kWarpsPerBlock * (33 * R + 2) * 4;
+  cudaError_t e = cudaFuncSetAttribute(k_rank<R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_rank<R, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
-  if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores);
+  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, rl_entries);
+  if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
   k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
   return cudaGetLastError();
 }
@@ -420,11 +433,11 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
   const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
   const bool w = all || pairwise == FM_PW_WILCOXON;
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
-  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, scores, sm_count, st);
-  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, scores, sm_count, st);
-  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, scores, sm_count, st);
-  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, scores, sm_count, st);
-  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, scores, sm_count, st);
-  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, scores, sm_count, st);
+  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st);
   return cudaErrorInvalidValue;
 }
