@@ -3,6 +3,7 @@
 // across the edge, no CPU scoring path: every score comes from the kernels in this directory.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -564,6 +565,7 @@ void fm_batch_free(fm_batch *b) {
 // ------------------------------------------------------------------ scoring
 
 static void result_release(fm_result *r) {
+  if (!r->ctx) { delete r; return; }
   cudaStream_t st = r->ctx->stream;
   void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts,
                   r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo, r->d_anom_off, r->d_anom_idx, r->d_anom_val};
@@ -574,19 +576,28 @@ static void result_release(fm_result *r) {
   delete r;
 }
 
-static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
+static int validate_params(fm_ctx *ctx, const fm_params *p) {
   if (p->algorithms & ~FM_ALG_ALL) return set_err(ctx, FM_E_INVALID, "unknown algorithm bits");
   if ((p->algorithms & FM_ALG_HW) && (p->period < 32 || p->period > 2048))
     return set_err(ctx, FM_E_UNSUPPORTED, "Holt-Winters period must be between 32 and 2048 samples");
   if (p->pairwise > FM_PW_KRUSKAL) return set_err(ctx, FM_E_INVALID, "unknown pairwise algorithm");
   if (p->band_algorithm && (!(p->band_algorithm & p->algorithms) || (p->band_algorithm & (p->band_algorithm - 1))))
     return set_err(ctx, FM_E_INVALID, "band_algorithm must be one enabled FM_ALG_* bit");
-  const bool do_rank = p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0;
-  if (do_rank && std::max(b->max_base, b->max_cur) > 1024)
-    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 1024 samples");
+  return FM_OK;
+}
 
-  fm_result *r = new (std::nothrow) fm_result;
-  if (!r) return FM_E_NOMEM;
+#define FM_R(expr)                                                                              \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      cudaGetLastError();                                                                       \
+      return set_err(ctx, _e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,             \
+                     std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
+    }                                                                                           \
+  } while (0)
+
+// result buffers for a batch of n units / ns services, cleared, parameters resolved and uploaded
+static int result_alloc(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result *r) {
   r->ctx = ctx;
   r->batch = b;
   r->n_units = b->n_units;
@@ -595,16 +606,6 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   r->params = *p;
   cudaStream_t st = ctx->stream;
   const uint64_t n = b->n_units, ns = b->n_services;
-#define FM_R(expr)                                                                              \
-  do {                                                                                          \
-    cudaError_t _e = (expr);                                                                    \
-    if (_e != cudaSuccess) {                                                                    \
-      cudaGetLastError();                                                                       \
-      result_release(r);                                                                        \
-      return set_err(ctx, _e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,             \
-                     std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
-    }                                                                                           \
-  } while (0)
   for (auto &e : r->ev) FM_R(cudaEventCreate(&e));
   FM_R(cudaMallocAsync(&r->d_params, sizeof(DevParams), st));
   FM_R(cudaMallocAsync(&r->d_scores, (n + 1) * sizeof(fm_series_score), st));
@@ -624,23 +625,51 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   FM_R(cudaMemsetAsync(r->d_scores, 0, (n + 1) * sizeof(fm_series_score), st));
   FM_R(cudaMemsetAsync(r->d_counts, 0, (4 * ns + 4) * sizeof(uint32_t), st));
   FM_R(cudaMemsetAsync(r->d_worst, 0, (ns + 1) * sizeof(unsigned long long), st));
+  return FM_OK;
+}
 
-  const DevBatch db = dev_view(b);
-  FM_R(cudaEventRecord(r->ev[1], st));
-  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), r->d_scores, ctx->sm_count, st));
-  FM_R(cudaEventRecord(r->ev[2], st));
+// launch the scoring kernels over units [i0, i1) of the batch (results land at the same indices)
+static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_params *p, uint64_t i0, uint64_t i1,
+                        bool timed) {
+  cudaStream_t st = ctx->stream;
+  const bool do_rank = p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0;
+  DevBatch db = dev_view(b);
+  db.n_units = i1 - i0;
+  db.offsets += i0;
+  db.seg_lens += 3 * i0;
+  db.service_id += i0;
+  db.metric_type += i0;
+  db.first_unit += i0;
+  fm_series_score *scores = r->d_scores + i0;
+  uint32_t *ustat = r->d_unit_status + i0, *upts = r->d_unit_points + i0;
+  if (timed) FM_R(cudaEventRecord(r->ev[1], st));
+  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), scores, ctx->sm_count, st));
+  if (timed) FM_R(cudaEventRecord(r->ev[2], st));
   const bool band_in_kband = (p->band_algorithm & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES)) != 0;
-  FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, r->d_scores, r->d_unit_status, r->d_unit_points,
+  FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, scores, ustat, upts,
                       band_in_kband ? r->d_band_up : nullptr, band_in_kband ? r->d_band_lo : nullptr, st));
   if (p->algorithms & FM_ALG_HW)
-    FM_R(fm_launch_hw(db, r->d_params, p->period, r->d_scores, r->d_unit_status, r->d_unit_points,
+    FM_R(fm_launch_hw(db, r->d_params, p->period, scores, ustat, upts,
                       p->band_algorithm == FM_ALG_HW ? r->d_band_up : nullptr,
                       p->band_algorithm == FM_ALG_HW ? r->d_band_lo : nullptr, ctx->sm_count, st));
-  FM_R(cudaEventRecord(r->ev[3], st));
-  fm_launch_verdict_reduce(db, r->d_unit_status, r->d_unit_points, (uint32_t)ns, r->d_counts, r->d_worst, st);
+  if (timed) FM_R(cudaEventRecord(r->ev[3], st));
+  fm_launch_verdict_reduce(db, ustat, upts, r->n_services, r->d_counts, r->d_worst, st);
   FM_R(cudaGetLastError());
-  FM_R(cudaEventRecord(r->ev[4], st));
+  if (timed) FM_R(cudaEventRecord(r->ev[4], st));
+  return FM_OK;
+}
 #undef FM_R
+
+static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
+  int rc = validate_params(ctx, p);
+  if (rc) return rc;
+  if (p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0 && std::max(b->max_base, b->max_cur) > 1024)
+    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 1024 samples");
+  fm_result *r = new (std::nothrow) fm_result;
+  if (!r) return FM_E_NOMEM;
+  rc = result_alloc(ctx, b, p, r);
+  if (rc == FM_OK) rc = launch_range(ctx, r, b, p, 0, b->n_units, true);
+  if (rc) { result_release(r); return rc; }
   *out = r;
   return FM_OK;
 }
@@ -816,23 +845,114 @@ void fm_result_free(fm_result *r) {
   result_release(r);
 }
 
-// One-shot host-in / host-out scoring (the call a Go worker makes per sweep).
-int fm_score_host(fm_ctx *ctx, const fm_csr *host_csr, const fm_params *p, uint32_t n_services, fm_verdict *verdicts) {
-  if (!ctx || !host_csr || !p || !verdicts) return FM_E_INVALID;
-  fm_batch *b = nullptr;
-  int rc = fm_batch_from_csr(ctx, host_csr, &b);
+// One-shot host-in / host-out scoring (the call a Go worker makes per sweep).  The upload is
+// chunked on a second stream and each chunk is scored as soon as it has landed, so PCIe and the
+// kernels overlap; with pinned input (fm_host_alloc) the call runs at PCIe speed.
+int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_services, fm_verdict *verdicts) {
+  if (!ctx || !h || !p || !verdicts || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return FM_E_INVALID;
+  std::unique_lock<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = validate_params(ctx, p);
   if (rc) return rc;
-  if (n_services < b->n_services) { fm_batch_free(b); return set_err(ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1"); }
-  b->n_services = n_services;
-  fm_result *r = nullptr;
-  rc = fm_score(ctx, b, p, &r);
-  if (rc == FM_OK) {
-    uint64_t n = 0;
-    rc = fm_result_verdicts(r, verdicts, n_services, &n);
-    fm_result_free(r);
+  fm_batch tb;  // transient, device arrays from the stream-ordered pool
+  tb.ctx = ctx;
+  tb.owns = false;
+  bool aligned;
+  uint64_t used;
+  rc = scan_host_csr(ctx, h, &aligned, &used, &tb);
+  if (rc) return rc;
+  if (n_services < tb.n_services) return set_err(ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1");
+  tb.n_services = n_services;
+  if (!aligned || h->n_units == 0 ||
+      (p->pairwise != FM_PW_NONE && tb.max_base > 0 && tb.max_cur > 0 && std::max(tb.max_base, tb.max_cur) > 1024)) {
+    // unaligned input has to be re-packed first (and unsupported shapes report their error): plain path
+    g.unlock();
+    fm_batch *b = nullptr;
+    rc = fm_batch_from_csr(ctx, h, &b);
+    if (rc) return rc;
+    b->n_services = n_services;
+    fm_result *r = nullptr;
+    rc = fm_score(ctx, b, p, &r);
+    if (rc == FM_OK) {
+      uint64_t n = 0;
+      rc = fm_result_verdicts(r, verdicts, n_services, &n);
+      fm_result_free(r);
+    }
+    fm_batch_free(b);
+    return rc;
   }
-  fm_batch_free(b);
-  return rc;
+  const uint64_t n = h->n_units, n_vals = (uint64_t)h->offsets[n];
+  cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
+  fm_result *r = new (std::nothrow) fm_result;
+  if (!r) return FM_E_NOMEM;
+  std::vector<cudaEvent_t> evs;
+  cudaEvent_t ev_alloc = nullptr;
+  auto cleanup = [&]() {
+    cudaStreamSynchronize(cs);
+    cudaStreamSynchronize(st);
+    for (void *q : {(void *)tb.d_values, (void *)tb.d_offsets, (void *)tb.d_seg, (void *)tb.d_sid, (void *)tb.d_mt})
+      if (q) cudaFreeAsync(q, st);
+    for (auto e : evs) cudaEventDestroy(e);
+    if (ev_alloc) cudaEventDestroy(ev_alloc);
+    result_release(r);
+  };
+#define FM_H(expr)                                                                              \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      cudaGetLastError();                                                                       \
+      cleanup();                                                                                \
+      return set_err(ctx, _e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,             \
+                     std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
+    }                                                                                           \
+  } while (0)
+  FM_H(cudaMallocAsync(&tb.d_values, (n_vals + 32) * sizeof(float), st));
+  FM_H(cudaMallocAsync(&tb.d_offsets, (n + 1) * sizeof(int64_t), st));
+  FM_H(cudaMallocAsync(&tb.d_seg, (3 * n + 1) * sizeof(uint32_t), st));
+  FM_H(cudaMallocAsync(&tb.d_sid, (n + 1) * sizeof(uint32_t), st));
+  FM_H(cudaMallocAsync(&tb.d_mt, n + 1, st));
+  tb.n_units = n;
+  tb.n_values = n_vals + 32;
+  tb.sealed = true;
+  FM_H(cudaMemsetAsync(tb.d_values + n_vals, 0, 32 * sizeof(float), st));
+  if (!h->service_id) FM_H(cudaMemsetAsync(tb.d_sid, 0, n * sizeof(uint32_t), st));
+  if (!h->metric_type) FM_H(cudaMemsetAsync(tb.d_mt, 0, n, st));
+  rc = result_alloc(ctx, &tb, p, r);
+  if (rc) { cleanup(); return rc; }
+  // the copy stream may only touch the new buffers once the pool allocations are ordered before it
+  FM_H(cudaEventCreateWithFlags(&ev_alloc, cudaEventDisableTiming));
+  FM_H(cudaEventRecord(ev_alloc, st));
+  FM_H(cudaStreamWaitEvent(cs, ev_alloc, 0));
+  uint64_t target_bytes = 256ull << 20;  // ~256 MiB of samples per chunk
+  if (const char *env = getenv("FOREMAST_GPU_CHUNK_BYTES")) target_bytes = std::max<uint64_t>(4096, strtoull(env, nullptr, 10));
+  uint64_t i0 = 0;
+  while (i0 < n) {
+    uint64_t i1 = i0 + 1;
+    while (i1 < n && (uint64_t)(h->offsets[i1] - h->offsets[i0]) * sizeof(float) < target_bytes) ++i1;
+    if (n - i1 < 64) i1 = n;
+    const uint64_t v0 = (uint64_t)h->offsets[i0], v1 = (uint64_t)h->offsets[i1], cnt = i1 - i0;
+    if (v1 > v0) FM_H(cudaMemcpyAsync(tb.d_values + v0, h->values + v0, (v1 - v0) * sizeof(float), cudaMemcpyHostToDevice, cs));
+    FM_H(cudaMemcpyAsync(tb.d_offsets + i0, h->offsets + i0, (cnt + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, cs));
+    FM_H(cudaMemcpyAsync(tb.d_seg + 3 * i0, h->seg_lens + 3 * i0, 3 * cnt * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+    if (h->service_id) FM_H(cudaMemcpyAsync(tb.d_sid + i0, h->service_id + i0, cnt * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+    if (h->metric_type) FM_H(cudaMemcpyAsync(tb.d_mt + i0, h->metric_type + i0, cnt, cudaMemcpyHostToDevice, cs));
+    cudaEvent_t ev;
+    FM_H(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    evs.push_back(ev);
+    FM_H(cudaEventRecord(ev, cs));
+    FM_H(cudaStreamWaitEvent(st, ev, 0));
+    rc = launch_range(ctx, r, &tb, p, i0, i1, false);
+    if (rc) { cleanup(); return rc; }
+    i0 = i1;
+  }
+  fm_launch_verdict_finalize(n_services, r->d_counts, r->d_worst, r->d_verdicts, st);
+  FM_H(cudaGetLastError());
+  if (n_services)
+    FM_H(cudaMemcpyAsync(verdicts, r->d_verdicts, n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, st));
+  FM_H(cudaStreamSynchronize(st));
+#undef FM_H
+  cleanup();
+  return FM_OK;
 }
 
 }  // extern "C"

@@ -239,6 +239,22 @@ def test_bulk_csr_ingest_and_realignment(ctx, oracle):
     b2.free()
 
 
+def test_score_host_pipelined_chunks(ctx, oracle, monkeypatch):
+    """fm_score_host on an aligned CSR: chunked upload overlapped with scoring must give the same
+    verdicts as the oracle, for many small chunks and for one big one."""
+    h = oracle.synth(3000, 64, 40, 40, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, units_per_service=7)
+    p = full_params(oracle)
+    ref, _, _ = oracle.score(h, p)
+    want = oracle.verdicts(h, ref, h.n_services).tobytes()
+    for chunk in ("16384", "100000", None):
+        if chunk:
+            monkeypatch.setenv("FOREMAST_GPU_CHUNK_BYTES", chunk)
+        else:
+            monkeypatch.delenv("FOREMAST_GPU_CHUNK_BYTES", raising=False)
+        assert ctx.score_host(h, p).tobytes() == want
+        assert ctx.score_host(h, p, h.n_services + 5)[:h.n_services].tobytes() == want
+
+
 def test_bands_materialised(ctx, oracle):
     b = ctx.batch_synth(200, 300, 0, 45, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
     host = b.download()
