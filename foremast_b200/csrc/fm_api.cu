@@ -663,8 +663,8 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
 static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
   int rc = validate_params(ctx, p);
   if (rc) return rc;
-  if (p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0 && std::max(b->max_base, b->max_cur) > 1024)
-    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 1024 samples");
+  if (p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0 && std::max(b->max_base, b->max_cur) > 2048)
+    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 2048 samples");
   fm_result *r = new (std::nothrow) fm_result;
   if (!r) return FM_E_NOMEM;
   rc = result_alloc(ctx, b, p, r);
@@ -864,7 +864,7 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
   if (n_services < tb.n_services) return set_err(ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1");
   tb.n_services = n_services;
   if (!aligned || h->n_units == 0 ||
-      (p->pairwise != FM_PW_NONE && tb.max_base > 0 && tb.max_cur > 0 && std::max(tb.max_base, tb.max_cur) > 1024)) {
+      (p->pairwise != FM_PW_NONE && tb.max_base > 0 && tb.max_cur > 0 && std::max(tb.max_base, tb.max_cur) > 2048)) {
     // unaligned input has to be re-packed first (and unsupported shapes report their error): plain path
     g.unlock();
     fm_batch *b = nullptr;

@@ -209,7 +209,7 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
 // lost 4-5 issue slots per issued instruction to fetch stalls), and both are ALU-bound, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
 template <int R, int PHASE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) k_rank(DevBatch b, const DevParams *__restrict__ dp,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(DevBatch b, const DevParams *__restrict__ dp,
                                                               fm_series_score *__restrict__ scores, const int tile_words,
                                                               const int kRl) {
   // PHASE 0 keeps the compile-time tile (one tile per warp is small anyway; a run-time size cost it
@@ -426,7 +426,7 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
 
 }  // namespace
 
-// max_seg = longest baseline / current segment in the batch; segments above 1024 samples are
+// max_seg = longest baseline / current segment in the batch; segments above 2048 samples are
 // not ranked by this kernel (the caller reports FM_E_UNSUPPORTED).
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_seg,
                            fm_series_score *scores, int sm_count, cudaStream_t st) {
@@ -439,5 +439,6 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
   if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st);
   if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st);
   if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 2048) return launch<64>(b, dp, w, pooled, max_seg, scores, sm_count, st);
   return cudaErrorInvalidValue;
 }

@@ -119,7 +119,8 @@ def test_rank_cases_fixture(ctx, oracle, golden_dir):
 
 
 @pytest.mark.parametrize("shape,n", [((0, 60, 30), 5), ((0, 720, 720), 3000), ((1440, 0, 60), 2000),
-                                      ((300, 100, 90), 4097), ((10080, 30, 30), 300), ((0, 1024, 1024), 257)])
+                                      ((300, 100, 90), 4097), ((10080, 30, 30), 300), ((0, 1024, 1024), 257),
+                                      ((0, 2048, 1500), 131), ((40, 1025, 33), 65)])
 def test_score_parity_on_synthetic_batches(ctx, oracle, shape, n):
     flags = abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES
     b = ctx.batch_synth(n, *shape, units_per_service=80 if n > 100 else 5, n_metric_types=8 if n > 5 else 5, flags=flags)
@@ -152,7 +153,7 @@ def test_rolling_window_sizes(ctx, oracle, window):
 
 
 @pytest.mark.parametrize("shape,period,n", [((400, 0, 90), 96, 600), ((10080, 0, 60), 1440, 150),
-                                            ((2900, 30, 1000), 1440, 100), ((64, 0, 33), 32, 300),
+                                            ((2900, 30, 1500), 1440, 100), ((64, 0, 33), 32, 300),
                                             ((5000, 40, 40), 2048, 64)])
 def test_holt_winters(ctx, oracle, shape, period, n):
     """BASELINE.json configs[3]: Holt-Winters seasonal (period 1440, 7-day history), continuous mode.
