@@ -111,19 +111,27 @@ void resolve_params(const fm_params *p, DevParams *d) {
   d->alpha = p->alpha;
   d->beta = p->beta;
   d->gamma = p->gamma;
-  {  // powers of the Holt-Winters level/trend transition matrix (fm_hw.cu)
+  {  // powers of the Holt-Winters level/trend transition matrix (fm_hw.cu): with k = period/32 samples
+     // per lane, hw_lane[l] = A^(k*l) (identity for lane 0) and hw_pow[i] = A^(k*2^i)
     const double a = p->alpha, ab = p->alpha * p->beta;
-    double A[4] = {1.0 - a, 1.0 - a, -ab, 1.0 - ab}, P[4] = {A[0], A[1], A[2], A[3]};
+    const double A[4] = {1.0 - a, 1.0 - a, -ab, 1.0 - ab};
     auto mul = [](const double *x, const double *y, double *o) {
       const double r[4] = {x[0] * y[0] + x[1] * y[2], x[0] * y[1] + x[1] * y[3], x[2] * y[0] + x[3] * y[2], x[2] * y[1] + x[3] * y[3]};
       for (int i = 0; i < 4; ++i) o[i] = r[i];
     };
-    for (int l = 0; l < 32; ++l) {  // A^(l+1)
+    const uint32_t k = p->period >= 32 ? p->period / 32 : 1;
+    double Ak[4] = {1.0, 0.0, 0.0, 1.0};
+    for (uint32_t i = 0; i < k; ++i) mul(Ak, A, Ak);
+    double P[4] = {1.0, 0.0, 0.0, 1.0};
+    for (int l = 0; l < 32; ++l) {  // A^(k*l)
       for (int i = 0; i < 4; ++i) d->hw_lane[4 * l + i] = P[i];
-      mul(P, A, P);
+      mul(P, Ak, P);
     }
-    for (int i = 0; i < 5; ++i)
-      for (int j = 0; j < 4; ++j) d->hw_pow[4 * i + j] = d->hw_lane[4 * ((1 << i) - 1) + j];
+    double Q[4] = {Ak[0], Ak[1], Ak[2], Ak[3]};
+    for (int i = 0; i < 5; ++i) {   // A^(k*2^i)
+      for (int j = 0; j < 4; ++j) d->hw_pow[4 * i + j] = Q[j];
+      mul(Q, Q, Q);
+    }
   }
   for (int i = 0; i < FM_MAX_METRIC_TYPES; ++i) {
     const fm_metric_rule &r = p->rules[i].bound ? p->rules[i] : p->rules[0];  // D16

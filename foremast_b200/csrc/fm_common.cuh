@@ -37,7 +37,8 @@ struct DevParams {
   uint32_t min_anomaly_points, ma_window, period, band_algorithm;
   double alpha, beta, gamma;
   DevRule rules[FM_MAX_METRIC_TYPES];
-  // Holt-Winters level/trend transition A = [[1-a, 1-a], [-ab, 1-ab]]: A^(2^i) and A^(lane+1), row-major
+  // Holt-Winters level/trend transition A = [[1-a, 1-a], [-ab, 1-ab]], k = period/32:
+  // hw_pow[i] = A^(k*2^i), hw_lane[l] = A^(k*l), row-major
   double hw_pow[5 * 4];
   double hw_lane[32 * 4];
 };
@@ -56,6 +57,10 @@ __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_m
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
   unsigned s = (unsigned)__cvta_generic_to_shared(smem);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>

@@ -3,22 +3,27 @@
 // (foremast-barrelman/pkg/client/metrics/metricsquery.go:95-97), period 1440 = one day at 60 s.
 //
 // Mapping: ONE WARP PER SERIES-WINDOW.  The seasonal array (period fp64 values, 11.25 KB at 1440)
-// lives in shared memory, so a thread-per-series layout is impossible; instead the warp walks the
-// stream 32 samples at a time.  Given last season's S, level and trend obey a 2-state linear
-// recurrence with constant matrix
+// lives in shared memory, so a thread-per-series layout is impossible.  Given last season's S,
+// level and trend obey a 2-state linear recurrence with constant matrix
 //     [l'; b'] = A [l; b] + g * (x - S),  A = [[1-a, 1-a], [-ab, 1-ab]],  g = [a; ab]
-// so each 32-sample tile is an inclusive warp scan of affine maps: five SHFL.UP steps with the
-// precomputed powers A^1..A^16, then the carry from the previous tile enters through A^(lane+1).
-// The season update S[i] += g1*e is pointwise once the one-step error e is known.  fp64
-// throughout; the scan re-associates the sums, so floats match the sequential oracle to ~1e-15
-// relative (tested at 1e-5), not bit for bit.
+// The stream is cut into super-tiles of 32*k samples (k = period/32, so a super-tile never
+// touches a seasonal slot twice) and each lane owns k CONSECUTIVE samples of it:
+//   pass 1  every lane runs the recurrence over its k samples from a zero state (sequential,
+//           5 fp64 ops per sample, no shuffles) -> its chunk's affine offset u;
+//   scan    one inclusive warp scan of the 32 offsets with the precomputed A^(k*2^i), plus the
+//           carry of the previous super-tile through A^(k*lane) -> the true state entering each chunk;
+//   pass 2  every lane re-runs its k samples from that state: one-step error, season update,
+//           residual sum / flags.
+// This reduce-then-scan form does ~12 fp64 ops per sample; the first version scanned every
+// 32-sample tile across lanes (five SHFL+2x2-matvec rounds per tile) and was 5x slower.
+// fp64 throughout; the scan re-associates the sums, so floats match the sequential oracle to
+// ~1e-15 relative (tested at 1e-5), not bit for bit.
 // Algorithmic bytes per unit: 4*(n_model + n_cur) + 8 + 12 + 32.
 #include "fm_common.cuh"
 
 namespace {
 
 constexpr int kWarpsPerBlock = 4;
-constexpr int kGroup = 8;  // tiles whose loads are issued together (8 x 128 B in flight per warp)
 
 struct V2 { double l, b; };
 
@@ -39,13 +44,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
                                                             const unsigned long long *__restrict__ emit_off,
                                                             uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val) {
   constexpr bool BANDS = MODE == 1, EMIT = MODE == 2;
-  extern __shared__ double s_season[];  // [warps][period]
+  extern __shared__ double s_dyn[];  // [warps][period] seasonals, then [warps][32*k] fp32 samples
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
-  const uint32_t m = dp->period;
-  double *const S = s_season + (size_t)warp * m;
+  const uint32_t m = dp->period, k = m / 32, lt = 32 * k;
+  double *const S = s_dyn + (size_t)warp * m;
+  float *const X = reinterpret_cast<float *>(s_dyn + (size_t)kWarpsPerBlock * m) + (size_t)warp * lt;
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta, g1 = dp->gamma * (1.0 - dp->alpha);
-  const double *const Apow = dp->hw_pow;       // A^(2^i), i = 0..4
-  const double *const Alane = dp->hw_lane + 4 * lane;  // A^(lane+1)
+  const double *const Apow = dp->hw_pow;               // A^(k*2^i), i = 0..4
+  const double *const Alane = dp->hw_lane + 4 * lane;  // A^(k*lane)
 
   for (uint64_t u = (uint64_t)blockIdx.x * kWarpsPerBlock + warp; u < b.n_units;
        u += (uint64_t)gridDim.x * kWarpsPerBlock) {
@@ -62,17 +68,17 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
     }
     const uint32_t c0 = nh + nb, n_stream = ns + nc;
     const float *unit = b.values + off;
-    auto sample = [&](uint32_t q) -> double { return (double)unit[q < ns ? a0 + q : c0 + (q - ns)]; };
+    auto sample = [&](uint32_t q) -> float { return unit[q < ns ? a0 + q : c0 + (q - ns)]; };
 
     uint32_t st = scores[u].status;
     const DevRule &dr = dp->rules[b.metric_type[u] < FM_MAX_METRIC_TYPES ? b.metric_type[u] : 0];
-    const double k = (st & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
+    const double kk = (st & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
     const double mlb = dr.min_lower_bound;
     const uint32_t bound = dr.bound;
 
     // ---- initialisation from the first two seasons (D5)
     double s0 = 0.0, s1 = 0.0;
-    for (uint32_t i = lane; i < m; i += 32) { s0 += sample(i); s1 += sample(m + i); }
+    for (uint32_t i = lane; i < m; i += 32) { s0 += (double)sample(i); s1 += (double)sample(m + i); }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       s0 += __shfl_xor_sync(0xffffffffu, s0, o);
@@ -83,95 +89,142 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
     carry.l = L0;
     carry.b = (M2 - L0) / (double)m;
     __syncwarp();
-    for (uint32_t i = lane; i < m; i += 32) S[i] = sample(i) - L0;
-    __syncwarp();
+    for (uint32_t i = lane; i < m; i += 32) S[i] = (double)sample(i) - L0;
 
     double sse = 0.0, sigma = 0.0;
     bool sigma_ready = false;
     uint32_t n_anom = 0, first = FM_NONE_IDX;
-    uint32_t idx = lane % m;  // (m + tile*32 + lane) mod m, kept incrementally
-    const uint32_t n_tiles = (n_stream - m + 31) / 32;
 
-    for (uint32_t tg = 0; tg < n_tiles; tg += kGroup) {
-      double xs[kGroup];
-#pragma unroll
-      for (int g = 0; g < kGroup; ++g) {
-        const uint32_t q = m + (tg + g) * 32 + lane;
-        xs[g] = q < n_stream ? sample(q) : 0.0;
-      }
-#pragma unroll
-      for (int g = 0; g < kGroup; ++g) {
-        const uint32_t tile = tg + g;
-        if (tile >= n_tiles) break;
-        const uint32_t q = m + tile * 32 + lane;
-        const bool valid = q < n_stream;
-        const double x = xs[g];
-        const double seas = S[idx];
-        const double y = valid ? x - seas : 0.0;
-        // inclusive scan of u_t = g*y_t under v -> A v
-        V2 uv;
-        uv.l = alpha * y;
-        uv.b = ab * y;
-#pragma unroll
-        for (int i = 0; i < 5; ++i) {
-          const int o = 1 << i;
-          V2 p;
-          p.l = __shfl_up_sync(0xffffffffu, uv.l, o);
-          p.b = __shfl_up_sync(0xffffffffu, uv.b, o);
-          if ((int)lane >= o) {
-            const V2 t = matvec(Apow + 4 * i, p);
-            uv.l += t.l;
-            uv.b += t.b;
-          }
+    for (uint32_t q0 = m; q0 < n_stream; q0 += lt) {
+      // stage the super-tile (coalesced) and find this lane's chunk
+      __syncwarp();
+      {  // 4-byte async copies, all in flight together (segments are only 4 B aligned in general)
+        const uint32_t nv = min(lt, n_stream - q0);
+#pragma unroll 9
+        for (uint32_t i = lane; i < nv; i += 32) {
+          const uint32_t q = q0 + i;
+          cp_async4(X + i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
         }
+        cp_async_commit();
+        cp_async_wait<0>();
+      }
+      __syncwarp();
+      const uint32_t p0 = lane * k, qa = q0 + p0;           // first local / stream position of the chunk
+      const uint32_t idx0 = (qa) % m;                        // its seasonal slot
+      const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
+      // pass 1: chunk offset from a zero state
+      V2 uo;
+      uo.l = 0.0;
+      uo.b = 0.0;
+      {
+        // (chunks past the end of the stream only feed lanes that are past the end too)
+        uint32_t idx = idx0;
+#pragma unroll 5
+        for (uint32_t i = 0; i < kv; ++i) {
+          const double y = (double)X[p0 + i] - S[idx];
+          const double t = uo.l + uo.b, w = y - t;
+          uo.l = fma(alpha, w, t);
+          uo.b = fma(ab, w, uo.b);
+          if (++idx == m) idx = 0;
+        }
+      }
+      // inclusive scan of the chunk maps v -> A^k v + u
+      V2 inc = uo;
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int o = 1 << i;
+        V2 p;
+        p.l = __shfl_up_sync(0xffffffffu, inc.l, o);
+        p.b = __shfl_up_sync(0xffffffffu, inc.b, o);
+        if ((int)lane >= o) {
+          const V2 t = matvec(Apow + 4 * i, p);
+          // inc covers the last min(o, lane+1)... chunks ending at this lane: shift the earlier block through them
+          inc.l += t.l;
+          inc.b += t.b;
+        }
+      }
+      V2 vin;  // state entering this lane's chunk
+      vin.l = __shfl_up_sync(0xffffffffu, inc.l, 1);
+      vin.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
+      if (lane == 0) { vin.l = 0.0; vin.b = 0.0; }
+      {
         const V2 cv = matvec(Alane, carry);
-        V2 v;  // state after sample q
-        v.l = uv.l + cv.l;
-        v.b = uv.b + cv.b;
-        V2 pv;  // state before sample q
-        pv.l = __shfl_up_sync(0xffffffffu, v.l, 1);
-        pv.b = __shfl_up_sync(0xffffffffu, v.b, 1);
-        if (lane == 0) pv = carry;
-        const double f = (pv.l + pv.b) + seas;
-        const double e = x - f;
-        if (valid) S[idx] = fma(g1, e, seas);
-        const bool in_src = valid && q < ns, in_cur = valid && q >= ns;
-        if (in_src) sse = fma(e, e, sse);
-        const unsigned cur_mask = __ballot_sync(0xffffffffu, in_cur);
-        if (cur_mask) {
-          if (!sigma_ready) {  // the model window ends in this tile: close the residual sum first
+        vin.l += cv.l;
+        vin.b += cv.b;
+      }
+      // pass 2: the real recurrence over the chunk; flags collected in a 64-bit mask (k <= 64)
+      double l = vin.l, bb = vin.b;
+      unsigned long long fmask = 0ull;
+      uint32_t idx = idx0, i = 0;
+      const bool tile_has_cur = q0 + lt > ns;
+      for (int half = 0; half < 2; ++half) {
+        // half 0: samples of the model window; half 1: current samples (sigma must be final first)
+        const uint32_t i_end = half == 0 ? (qa < ns ? min(kv, ns - qa) : 0u) : kv;
+#pragma unroll 5
+        for (; i < i_end; ++i) {
+          const double x = (double)X[p0 + i], seas = S[idx];
+          const double lb = l + bb, f = lb + seas, e = x - f;
+          l = fma(alpha, e, lb);
+          bb = fma(ab, e, bb);
+          S[idx] = fma(g1, e, seas);
+          if (half == 0) {
+            sse = fma(e, e, sse);
+          } else {
+            const double up = fma(kk, sigma, f);
+            double lo = fma(-kk, sigma, f);
+            lo = lo < mlb ? mlb : lo;
+            if (((bound & 1u) && x > up) || ((bound & 2u) && x < lo)) fmask |= 1ull << i;
+            if (BANDS) {
+              band_up[off + c0 + (qa + i - ns)] = (float)up;
+              band_lo[off + c0 + (qa + i - ns)] = (float)lo;
+            }
+          }
+          if (++idx == m) idx = 0;
+        }
+        if (half == 0) {
+          if (!tile_has_cur) break;
+          if (!sigma_ready) {  // the model window ends in this super-tile: close the residual sum first
             double t = sse;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
             sigma = sqrt(t / (double)(ns - m));
             sigma_ready = true;
           }
-          const double up = fma(k, sigma, f);
-          double lo = fma(-k, sigma, f);
-          lo = lo < mlb ? mlb : lo;
-          const bool flag = in_cur && (((bound & 1u) && x > up) || ((bound & 2u) && x < lo));
-          const unsigned fm = __ballot_sync(0xffffffffu, flag);
-          if (fm) {
-            if (n_anom == 0) first = (m + tile * 32 + (__ffs(fm) - 1)) - ns;
-            if (EMIT && flag) {
-              const unsigned long long at = emit_base + n_anom + __popc(fm & ((1u << lane) - 1u));
-              emit_idx[at] = q - ns;
-              emit_val[at] = (float)x;
-            }
-            n_anom += __popc(fm);
-          }
-          if (BANDS && in_cur) {
-            band_up[off + c0 + (q - ns)] = (float)up;
-            band_lo[off + c0 + (q - ns)] = (float)lo;
-          }
         }
-        // carry = state after the last valid sample of the tile
-        const uint32_t nvalid = min(32u, n_stream - (m + tile * 32));
-        carry.l = __shfl_sync(0xffffffffu, v.l, nvalid - 1);
-        carry.b = __shfl_sync(0xffffffffu, v.b, nvalid - 1);
-        idx += 32;
-        if (idx >= m) idx -= m;
-        __syncwarp();  // S[] written by this tile may be read by the next one when period < 64
+      }
+      // next super-tile's carry: the state after lane 31's chunk (only needed while tiles are full)
+      carry.l = __shfl_sync(0xffffffffu, l, 31);
+      carry.b = __shfl_sync(0xffffffffu, bb, 31);
+      if (tile_has_cur) {
+        const uint32_t cnt = __popcll(fmask);
+        uint32_t pre = cnt;  // exclusive prefix of flag counts over lanes (chunks are in stream order)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, pre, o);
+          if ((int)lane >= o) pre += t;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+        pre -= cnt;
+        if (total) {
+          const unsigned has = __ballot_sync(0xffffffffu, cnt != 0);
+          if (n_anom == 0) {
+            const int src = __ffs(has) - 1;
+            const uint32_t cand = qa + (uint32_t)(__ffsll((long long)fmask) - 1) - ns;
+            first = __shfl_sync(0xffffffffu, cand, src);
+          }
+          if (EMIT) {
+            unsigned long long mk = fmask;
+            uint32_t r = 0;
+            while (mk) {
+              const int bit = __ffsll((long long)mk) - 1;
+              mk &= mk - 1;
+              const unsigned long long at = emit_base + n_anom + pre + r++;
+              emit_idx[at] = qa + bit - ns;
+              emit_val[at] = X[p0 + bit];
+            }
+          }
+          n_anom += total;
+        }
       }
     }
     if (lane == 0 && !EMIT) {
@@ -199,7 +252,7 @@ static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t pe
   const uint64_t cap = (uint64_t)sm_count * 32;
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  const int smem = kWarpsPerBlock * (int)period * (int)sizeof(double);
+  const int smem = kWarpsPerBlock * ((int)period * (int)sizeof(double) + 32 * ((int)period / 32) * (int)sizeof(float));
   cudaError_t e = cudaFuncSetAttribute(k_hw<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_hw<MODE><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
