@@ -226,9 +226,10 @@ class Result:
         return counts.value, worst.value, ns.value
 
     def timings_ms(self):
-        ms = (C.c_float * 4)()
-        self.ctx._check(self.ctx._L.fm_result_timings(self._h, ms, 4))
-        return {"setup": ms[0], "rank": ms[1], "band": ms[2], "verdict": ms[3]}
+        ms = (C.c_float * 5)()
+        self.ctx._check(self.ctx._L.fm_result_timings(self._h, ms, 5))
+        return {"setup": ms[0], "rank_wilcoxon": ms[1], "rank_mw": ms[2], "rank": ms[1] + ms[2], "band": ms[3],
+                "verdict": ms[4]}
 
     def free(self):
         if self._h and self.ctx._h:

@@ -62,7 +62,7 @@ struct fm_result {
   float *d_anom_val = nullptr;
   uint64_t anom_total = 0;
   uint32_t anom_alg = 0;
-  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // start, pre-rank, post-rank, post-band, post-verdict
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // start, pre-rank, post-Wilcoxon, post-rank, post-band, post-verdict
 };
 
 namespace {
@@ -651,8 +651,12 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
   fm_series_score *scores = r->d_scores + i0;
   uint32_t *ustat = r->d_unit_status + i0, *upts = r->d_unit_points + i0;
   if (timed) FM_R(cudaEventRecord(r->ev[1], st));
-  if (do_rank) FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), scores, ctx->sm_count, st));
-  if (timed) FM_R(cudaEventRecord(r->ev[2], st));
+  if (do_rank)
+    FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), scores, ctx->sm_count, st,
+                        timed ? r->ev[2] : nullptr));
+  else if (timed)
+    FM_R(cudaEventRecord(r->ev[2], st));
+  if (timed) FM_R(cudaEventRecord(r->ev[3], st));
   const bool band_in_kband = (p->band_algorithm & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES)) != 0;
   FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, scores, ustat, upts,
                       band_in_kband ? r->d_band_up : nullptr, band_in_kband ? r->d_band_lo : nullptr, st));
@@ -660,10 +664,10 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
     FM_R(fm_launch_hw(db, r->d_params, p->period, scores, ustat, upts,
                       p->band_algorithm == FM_ALG_HW ? r->d_band_up : nullptr,
                       p->band_algorithm == FM_ALG_HW ? r->d_band_lo : nullptr, ctx->sm_count, st));
-  if (timed) FM_R(cudaEventRecord(r->ev[3], st));
+  if (timed) FM_R(cudaEventRecord(r->ev[4], st));
   fm_launch_verdict_reduce(db, ustat, upts, r->n_services, r->d_counts, r->d_worst, st);
   FM_R(cudaGetLastError());
-  if (timed) FM_R(cudaEventRecord(r->ev[4], st));
+  if (timed) FM_R(cudaEventRecord(r->ev[5], st));
   return FM_OK;
 }
 #undef FM_R
@@ -837,12 +841,12 @@ int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst,
 }
 
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap) {
-  if (!r || !ms || cap < 4) return FM_E_INVALID;
+  if (!r || !ms || cap < 5) return FM_E_INVALID;
   fm_ctx *ctx = r->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
-  FM_CUDA(ctx, cudaEventSynchronize(r->ev[4]));
-  for (int i = 0; i < 4; ++i) FM_CUDA(ctx, cudaEventElapsedTime(&ms[i], r->ev[i], r->ev[i + 1]));
+  FM_CUDA(ctx, cudaEventSynchronize(r->ev[5]));
+  for (int i = 0; i < 5; ++i) FM_CUDA(ctx, cudaEventElapsedTime(&ms[i], r->ev[i], r->ev[i + 1]));
   return FM_OK;
 }
 

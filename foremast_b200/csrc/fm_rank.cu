@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevPara
 
 template <int R>
 cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool want_pooled, uint32_t max_seg,
-                   fm_series_score *scores, int sm_count, cudaStream_t st) {
+                   fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
     // many more blocks than are resident: tie-heavy units take longer, the block scheduler evens it
   // out (a persistent 5-blocks-per-SM grid measured 19 % slower)
@@ -419,6 +419,7 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
   e = cudaFuncSetAttribute(k_rank<R, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, rl_entries);
+  if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
   if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
   k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
   return cudaGetLastError();
@@ -429,16 +430,16 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
 // max_seg = longest baseline / current segment in the batch; segments above 2048 samples are
 // not ranked by this kernel (the caller reports FM_E_UNSUPPORTED).
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_seg,
-                           fm_series_score *scores, int sm_count, cudaStream_t st) {
+                           fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon) {
   const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
   const bool w = all || pairwise == FM_PW_WILCOXON;
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
-  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st);
-  if (max_seg <= 2048) return launch<64>(b, dp, w, pooled, max_seg, scores, sm_count, st);
+  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 2048) return launch<64>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   return cudaErrorInvalidValue;
 }

@@ -300,8 +300,9 @@ int fm_scan_counts_static(const uint32_t *d_counts, uint64_t n, uint64_t *d_offs
  * counts = uint32[4*n_services] (n_units, n_unknown, n_anom_units, n_anom_points), summed;
  * worst  = uint64[n_services]   ((points << 32) | ~unit), maxed. */
 int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst, uint32_t *n_services);
-/* Device time of this fm_score in milliseconds per stage: {set-up (allocation, clears), rank kernel,
- * band kernel, verdict reduce}; CUDA events on the context's stream; cap >= 4. */
+/* Device time of this fm_score in milliseconds per stage: {set-up (allocation, clears), Wilcoxon
+ * rank kernel, Mann-Whitney/Kruskal rank kernel + p-values, band kernels, verdict reduce}; CUDA
+ * events on the context's stream; cap >= 5. */
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap);
 void fm_result_free(fm_result *r);
 
