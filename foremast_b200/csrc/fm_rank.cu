@@ -229,6 +229,24 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(De
   uint32_t *const sA = s_tiles + (size_t)warp * kTilesPerWarp * kTile, *const sB = PHASE == 0 ? sA : sA + kTile;
   uint16_t *const rlA = reinterpret_cast<uint16_t *>(s_tiles + (size_t)kWarpsPerBlock * kTilesPerWarp * kTile) + (size_t)warp * 2 * kRl;
   uint16_t *const rlB = rlA + kRl;
+  // PHASE 0 stages the NEXT unit's paired samples in shared memory with 4-byte cp.async while the
+  // current unit is being sorted in registers (kRl doubles as the per-segment capacity there)
+  float *const rawA = reinterpret_cast<float *>(s_tiles + (size_t)kWarpsPerBlock * kTilesPerWarp * kTile) + (size_t)warp * 2 * kRl;
+  float *const rawB = rawA + kRl;
+  auto stage_pairs = [&](uint64_t uu) {
+    if (uu < b.n_units) {
+      const int64_t o = b.offsets[uu];
+      const uint32_t h0 = b.seg_lens[3 * uu], n1 = b.seg_lens[3 * uu + 1], n2 = b.seg_lens[3 * uu + 2];
+      const uint32_t mm = min(min(n1, n2), (uint32_t)kRl);
+      const float *pa = b.values + o + h0, *pb = pa + n1;
+      for (uint32_t e = lane; e < mm; e += 32) {
+        cp_async4(rawA + e, pa + e);
+        cp_async4(rawB + e, pb + e);
+      }
+    }
+    cp_async_commit();
+  };
+  if (PHASE == 0) stage_pairs((uint64_t)blockIdx.x * kWarpsPerBlock + warp);
 
   // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
   const uint64_t n_rounds = (b.n_units + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
@@ -241,7 +259,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(De
       off = b.offsets[u];
       nh = b.seg_lens[3 * u]; nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2];
     }
-    {  // pull the next round's samples towards L2 while this round sorts
+    if (PHASE == 1) {  // pull the next round's samples towards L2 while this round sorts
       const uint64_t un = u + (uint64_t)gridDim.x * kWarpsPerBlock;
       if (un < b.n_units) {
         const int64_t offn = b.offsets[un];
@@ -266,17 +284,25 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(De
     // one sort routine, three passes: |d| keys (Wilcoxon), baseline, current
 #pragma unroll 1
     for (int seg = PHASE == 0 ? 0 : 1; seg < (PHASE == 0 ? 1 : 3); ++seg) {
+      if (PHASE == 0 && !run_w) {  // nothing to rank here, but the staging pipeline must keep moving
+        cp_async_wait<0>();
+        __syncwarp();
+        stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
+        continue;
+      }
       if (seg == 0 ? !run_w : !pooled) continue;
       uint32_t key[R];
       uint32_t n_valid;
       if (PHASE == 0) {
         uint32_t nz = 0;
+        cp_async_wait<0>();
+        __syncwarp();
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const uint32_t e = r * 32 + lane;
           uint32_t k = kKeySentinel;
           if (e < m) {
-            const float d = cur[e] - base[e];
+            const float d = rawB[e] - rawA[e];
             if (d != 0.0f) {
               k = (__float_as_uint(fabsf(d)) << 1) | (d < 0.0f ? 1u : 0u);
               ++nz;
@@ -285,6 +311,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(De
           key[r] = k;
         }
         n_valid = w_n = __reduce_add_sync(0xffffffffu, nz);
+        __syncwarp();  // every lane has its keys in registers: the staging buffers are free again
+        stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
       } else {
         const float *src = seg == 1 ? base : cur;
         n_valid = seg == 1 ? nb : nc;
@@ -413,12 +441,13 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
   const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
   const int tile_words = seg_cap + (seg_cap >> 5) + 2, rl_entries = (seg_cap + 2 + 1) & ~1;
   const int smem = kWarpsPerBlock * 2 * (tile_words * 4 + rl_entries * 2);
-  const int smem_w = kWarpsPerBlock * (33 * R + 2) * 4;
+  const int raw_cap = (seg_cap + 3) & ~3;
+  const int smem_w = kWarpsPerBlock * ((33 * R + 2) * 4 + 2 * raw_cap * 4);
   cudaError_t e = cudaFuncSetAttribute(k_rank<R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_rank<R, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, rl_entries);
+  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, raw_cap);
   if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
   if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
   k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);

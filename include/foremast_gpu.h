@@ -304,6 +304,7 @@ int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst,
  * rank kernel, Mann-Whitney/Kruskal rank kernel + p-values, band kernels, verdict reduce}; CUDA
  * events on the context's stream; cap >= 5. */
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap);
+/* Free results before the batch they were scored from (accessors read the batch's offsets). */
 void fm_result_free(fm_result *r);
 
 #ifdef __cplusplus

@@ -335,6 +335,39 @@ def test_device_csr_and_alignment_errors(ctx, oracle):
     assert ei.value.code == abi.E_ALIGN
 
 
+def test_sharded_batches_merge_like_multi_gpu(ctx, oracle):
+    """The N>1 path on one GPU: two shards with global unit ids (fm_batch_set_shard), their dense
+    per-service counters merged exactly as foremast_b200.dist does across ranks (sum / max on
+    tensors aliasing the library's buffers), verdicts finalised after the merge."""
+    import torch
+    from foremast_b200 import dist as fdist
+    n, ups = 3000, 40
+    p = full_params(oracle)
+    whole = oracle.synth(n, 64, 40, 40, units_per_service=ups, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+    ref, _, _ = oracle.score(whole, p)
+    want = oracle.verdicts(whole, ref, whole.n_services)
+    results = []
+    for rank in range(2):
+        lo, hi = fdist.shard_range(n, rank, 2, ups)
+        b = ctx.batch_synth(hi - lo, 64, 40, 40, units_per_service=ups, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES,
+                            first_unit=lo)
+        b.set_shard(lo, whole.n_services)
+        r = ctx.score(b, p)
+        r.sync()
+        results.append((b, r))
+    c0, w0 = fdist.alias_service_buffers(results[0][1])
+    c1, w1 = fdist.alias_service_buffers(results[1][1])
+    c0 += c1
+    torch.maximum(w0, w1, out=w0)
+    torch.cuda.synchronize()
+    got = results[0][1].verdicts()
+    assert got.tobytes() == want.tobytes()
+    assert (got["verdict"] == abi.V_UNHEALTH).any() and int(got["worst_unit"][got["verdict"] == abi.V_UNHEALTH].max()) >= n // 2
+    for b, r in results:
+        r.free()
+        b.free()
+
+
 def test_full_size_properties(ctx, oracle):
     """BASELINE.json headline shape: 1M series-windows x 1440 points (720 baseline + 720 current),
     all scorers.  Size-independent properties on everything, bit-exact oracle check on a sample."""
