@@ -147,7 +147,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{sample} units of the same workload per step, OpenMP over units"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    OUT.emit(json.dumps(line))
 
 
 def run_ours(args):
@@ -304,7 +304,7 @@ def run_ours(args):
             "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
                                 "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
         }
-        print(json.dumps(line))
+        OUT.emit(json.dumps(line))
     ctx.host_free(pin_ptr)
     batch.free()
     ctx.close()
@@ -312,7 +312,26 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+class QuietStdout:
+    """Everything that is not the result line goes to stderr: libraries (NCCL prints its version
+    on stdout) must not break the one-JSON-line contract.  emit() writes to the real stdout."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, line):
+        sys.stdout.flush()
+        os.write(self._saved, (line + "\n").encode())
+
+
+OUT = None
+
+
 def main():
+    global OUT
+    OUT = QuietStdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
