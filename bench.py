@@ -221,6 +221,40 @@ def run_ours(args):
                 ts.append(t)
         single_ms[name] = sum(ts) / len(ts)
 
+    # ---- the other BASELINE.json configs, device-resident, rank 0 only at N = 1 (parity for these
+    #      shapes is in tests/; here only their kernel times and roofline fractions)
+    other = {}
+    if world == 1 and not args.skip_configs:
+        def timed(make_batch, q, key, passes=4):
+            bb = make_batch()
+            ts = []
+            for i in range(2 + passes):
+                res = ctx.score(bb, q)
+                t = res.timings_ms()
+                res.free()
+                if i >= 2:
+                    ts.append(t[key])
+            info = bb.info()
+            bb.free()
+            return sum(ts) / len(ts), info
+        peak_gbs, _ = measured_peak()
+        # cfg2: 10k pods x 8 metrics x 1440-pt EWMA + double-exponential smoothing bands
+        q = bench_params(default_params()); q.algorithms = abi.ALG_EWMA | abi.ALG_DES; q.pairwise = abi.PW_NONE
+        ms, info = timed(lambda: ctx.batch_synth(80_000, 1380, 0, 60, units_per_service=8, n_metric_types=8,
+                                                 flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES), q, "band", 8)
+        nbytes = 80_000 * (4 * 1440 + 36)
+        other["cfg2_80k_x_1440_ewma_des"] = {"ms": ms, "series_windows_per_s": 80_000 / (ms * 1e-3), "achieved_gbs": nbytes / (ms * 1e-3) / 1e9,
+                                              "frac": nbytes / (ms * 1e-3) / 1e9 / peak_gbs, "shape": "1380 model + 60 current points"}
+        # cfg3: 1M series x 720-pt baseline-vs-canary rank tests = the rank stage of the headline step
+        # cfg4: 1M series Holt-Winters seasonal (period 1440, 7-day history)
+        q = bench_params(default_params()); q.algorithms = abi.ALG_HW; q.pairwise = abi.PW_NONE; q.period = 1440
+        n4 = args.hw_units
+        ms, info = timed(lambda: ctx.batch_synth(n4, 10_080, 0, 60, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
+                                                 flags=abi.SYNTH_ANOMALIES), q, "band", 3)
+        nbytes = n4 * (4 * 10_140 + 52)
+        other["cfg4_holt_winters_10080pt_period1440"] = {"units": n4, "ms": ms, "series_per_s": n4 / (ms * 1e-3),
+                                                         "achieved_gbs": nbytes / (ms * 1e-3) / 1e9, "frac": nbytes / (ms * 1e-3) / 1e9 / peak_gbs}
+
     # ---- end to end through the public one-shot call: pinned host CSR -> H2D -> score -> verdicts D2H
     host = batch.download()
     nbytes = host.values.nbytes
@@ -294,6 +328,7 @@ def run_ours(args):
                          "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
                          "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0},
             "kernels": kernels,
+            "other_configs": other,
             "cpu_baseline": ({"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
                               "sample": f"first {sample} units of rank 0's batch, one pass, {cpu_s:.2f} s"}
                              if cpu_rate is not None else None),
@@ -301,7 +336,8 @@ def run_ours(args):
                     "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps},
             # per step: k_rank (Wilcoxon), k_rank (MWU/Kruskal), k_rank_finalize, k_band, k_verdict_reduce,
             # k_verdict_finalize; the e2e call runs the first five once per ~256 MiB upload chunk
-            "gpu_launches": 6 * args.steps + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 3 * 8 * 2 + 1,
+            "gpu_launches": 6 * args.steps + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 3 * 8 * 2 + 1
+            + (10 * 3 + 5 * 4 + 2 if other else 0),
             "clocks": clocks,
             "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
                                 "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
@@ -343,6 +379,8 @@ def main():
     ap.add_argument("--cpu-units", type=int, default=131072, help="cpu_baseline sample (units)")
     ap.add_argument("--ref-units", type=int, default=65536, help="--impl reference: units per step")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--hw-units", type=int, default=1_000_000, help="cfg4 Holt-Winters units (10080 points each)")
+    ap.add_argument("--skip-configs", action="store_true", help="skip the extra cfg2 / cfg4 timings")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
