@@ -50,6 +50,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
   double *const S = s_dyn + (size_t)warp * m;
   float *const X = reinterpret_cast<float *>(s_dyn + (size_t)kWarpsPerBlock * m) + (size_t)warp * lt;
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta, g1 = dp->gamma * (1.0 - dp->alpha);
+  // A^2 and A*g for the two-samples-per-iteration form of the recurrence
+  const double a1 = 1.0 - alpha, d1 = 1.0 - ab;
+  const double a2[4] = {a1 * a1 - a1 * ab, a1 * a1 + a1 * d1, -ab * a1 - ab * d1, -ab * a1 + d1 * d1};
+  const double agl = a1 * alpha + a1 * ab, agb = -ab * alpha + d1 * ab;
   const double *const Apow = dp->hw_pow;               // A^(k*2^i), i = 0..4
   const double *const Alane = dp->hw_lane + 4 * lane;  // A^(k*lane)
 
@@ -100,10 +104,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
       __syncwarp();
       {  // 4-byte async copies, all in flight together (segments are only 4 B aligned in general)
         const uint32_t nv = min(lt, n_stream - q0);
+        if (q0 + nv <= ns || q0 >= ns) {  // the super-tile lies in one segment: one contiguous source
+          const float *src = unit + (q0 < ns ? a0 + q0 : c0 + (q0 - ns));
 #pragma unroll 9
-        for (uint32_t i = lane; i < nv; i += 32) {
-          const uint32_t q = q0 + i;
-          cp_async4(X + i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          for (uint32_t i = lane; i < nv; i += 32) cp_async4(X + i, src + i);
+        } else {
+          for (uint32_t i = lane; i < nv; i += 32) {
+            const uint32_t q = q0 + i;
+            cp_async4(X + i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          }
         }
         cp_async_commit();
         cp_async_wait<0>();
@@ -112,20 +121,46 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
       const uint32_t p0 = lane * k, qa = q0 + p0;           // first local / stream position of the chunk
       const uint32_t idx0 = (qa) % m;                        // its seasonal slot
       const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
+      // seasonal slot of local sample i; chunks that cross the end of the season take the slow loops
+      const bool wrap = __any_sync(0xffffffffu, idx0 + kv > m);
+      auto sidx = [&](uint32_t i) { const uint32_t j = idx0 + i; return j >= m ? j - m : j; };
       // pass 1: chunk offset from a zero state
       V2 uo;
       uo.l = 0.0;
       uo.b = 0.0;
       {
         // (chunks past the end of the stream only feed lanes that are past the end too)
-        uint32_t idx = idx0;
-#pragma unroll 5
-        for (uint32_t i = 0; i < kv; ++i) {
-          const double y = (double)X[p0 + i] - S[idx];
+        // Two samples per iteration: v'' = A^2 v + (A g y1 + g y2).  The bracket does not depend on
+        // the state, so the dependent chain is one 2x2 mat-vec per TWO samples instead of four
+        // dependent fp64 ops per sample -- this kernel is fp64-latency bound.
+        uint32_t i = 0;
+        if (!wrap) {
+          const float *xp = X + p0;
+          const double *sp = S + idx0;
+#pragma unroll 4
+          for (; i + 1 < kv; i += 2) {
+            const double y1 = (double)xp[i] - sp[i], y2 = (double)xp[i + 1] - sp[i + 1];
+            const double cl = fma(agl, y1, alpha * y2), cb = fma(agb, y1, ab * y2);
+            const double nl = fma(a2[0], uo.l, fma(a2[1], uo.b, cl));
+            const double nb2 = fma(a2[2], uo.l, fma(a2[3], uo.b, cb));
+            uo.l = nl;
+            uo.b = nb2;
+          }
+        } else {
+          for (; i + 1 < kv; i += 2) {
+            const double y1 = (double)X[p0 + i] - S[sidx(i)], y2 = (double)X[p0 + i + 1] - S[sidx(i + 1)];
+            const double cl = fma(agl, y1, alpha * y2), cb = fma(agb, y1, ab * y2);
+            const double nl = fma(a2[0], uo.l, fma(a2[1], uo.b, cl));
+            const double nb2 = fma(a2[2], uo.l, fma(a2[3], uo.b, cb));
+            uo.l = nl;
+            uo.b = nb2;
+          }
+        }
+        if (i < kv) {
+          const double y = (double)X[p0 + i] - S[sidx(i)];
           const double t = uo.l + uo.b, w = y - t;
           uo.l = fma(alpha, w, t);
           uo.b = fma(ab, w, uo.b);
-          if (++idx == m) idx = 0;
         }
       }
       // inclusive scan of the chunk maps v -> A^k v + u
@@ -155,13 +190,53 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
       // pass 2: the real recurrence over the chunk; flags collected in a 64-bit mask (k <= 64)
       double l = vin.l, bb = vin.b;
       unsigned long long fmask = 0ull;
-      uint32_t idx = idx0, i = 0;
+      uint32_t i = 0;
       const bool tile_has_cur = q0 + lt > ns;
       for (int half = 0; half < 2; ++half) {
         // half 0: samples of the model window; half 1: current samples (sigma must be final first)
         const uint32_t i_end = half == 0 ? (qa < ns ? min(kv, ns - qa) : 0u) : kv;
-#pragma unroll 5
+        // pairs: the state two samples ahead comes straight from A^2 (short dependent chain); the
+        // state one sample ahead, the two one-step errors and the season updates hang off it
+        auto pair_step = [&](uint32_t ii, const float *xq, double *sq1, double *sq2) {
+          const double x1 = (double)xq[0], x2 = (double)xq[1], s1 = *sq1, s2 = *sq2;
+          const double y1 = x1 - s1, y2 = x2 - s2;
+          const double lb1 = l + bb, e1 = y1 - lb1;
+          const double l1 = fma(alpha, e1, lb1), b1 = fma(ab, e1, bb);      // state after the first sample
+          const double cl = fma(agl, y1, alpha * y2), cb = fma(agb, y1, ab * y2);
+          const double l2 = fma(a2[0], l, fma(a2[1], bb, cl)), b2 = fma(a2[2], l, fma(a2[3], bb, cb));
+          const double lb2 = l1 + b1, e2 = y2 - lb2;
+          *sq1 = fma(g1, e1, s1);
+          *sq2 = fma(g1, e2, s2);
+          if (half == 0) {
+            sse = fma(e1, e1, sse);
+            sse = fma(e2, e2, sse);
+          } else {
+            const double f1 = lb1 + s1, f2 = lb2 + s2;
+            const double up1 = fma(kk, sigma, f1), up2 = fma(kk, sigma, f2);
+            double lo1 = fma(-kk, sigma, f1), lo2 = fma(-kk, sigma, f2);
+            lo1 = lo1 < mlb ? mlb : lo1;
+            lo2 = lo2 < mlb ? mlb : lo2;
+            if (((bound & 1u) && x1 > up1) || ((bound & 2u) && x1 < lo1)) fmask |= 1ull << ii;
+            if (((bound & 1u) && x2 > up2) || ((bound & 2u) && x2 < lo2)) fmask |= 2ull << ii;
+            if (BANDS) {
+              const int64_t at = off + c0 + (qa + ii - ns);
+              band_up[at] = (float)up1; band_lo[at] = (float)lo1;
+              band_up[at + 1] = (float)up2; band_lo[at + 1] = (float)lo2;
+            }
+          }
+          l = l2;
+          bb = b2;
+        };
+        if (!wrap) {
+          const float *xp = X + p0;
+          double *sp = S + idx0;
+#pragma unroll 2
+          for (; i + 1 < i_end; i += 2) pair_step(i, xp + i, sp + i, sp + i + 1);
+        } else {
+          for (; i + 1 < i_end; i += 2) pair_step(i, X + p0 + i, S + sidx(i), S + sidx(i + 1));
+        }
         for (; i < i_end; ++i) {
+          const uint32_t idx = sidx(i);
           const double x = (double)X[p0 + i], seas = S[idx];
           const double lb = l + bb, f = lb + seas, e = x - f;
           l = fma(alpha, e, lb);
@@ -179,7 +254,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
               band_lo[off + c0 + (qa + i - ns)] = (float)lo;
             }
           }
-          if (++idx == m) idx = 0;
         }
         if (half == 0) {
           if (!tile_has_cur) break;
