@@ -108,6 +108,11 @@ assert C.sizeof(Params) == 464
 assert C.sizeof(SynthConfig) == 48
 
 
+PROM_SERIES = np.dtype([("metric_off", "<u8"), ("metric_len", "<u8"), ("t0", "<f8"), ("step", "<f8"),
+                        ("first_value", "<u8"), ("n_values", "<u4"), ("reserved", "<u4")])
+assert PROM_SERIES.itemsize == 48
+
+
 class HostCsr:
     """A host-side ragged CSR batch (numpy arrays) in the layout of `fm_csr`."""
 

@@ -25,6 +25,8 @@ SYMBOLS = {
     "fm_timer_stop": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "fm_host_alloc": (C.c_int, [_P, C.c_uint64, _PP]),
     "fm_host_free": (None, [_P, _P]),
+    "fm_parse_prometheus_matrix": (C.c_int, [C.c_char_p, C.c_uint64, _P, C.c_uint32, C.POINTER(C.c_uint32), _P,
+                                              C.c_uint64, C.POINTER(C.c_uint64)]),
     "fm_batch_begin": (C.c_int, [_P, C.c_uint64, C.c_uint64, _PP]),
     "fm_batch_add_series": (C.c_int, [_P, C.POINTER(abi.SeriesMeta), _P, C.c_uint32, _P, C.c_uint32, _P, C.c_uint32]),
     "fm_batch_seal": (C.c_int, [_P]),

@@ -63,12 +63,39 @@ def query_window(url):
     return num("start", 0.0), num("end", 0.0), num("step", float(STEP_SECONDS))
 
 
+def parse_matrix_native(body):
+    """Response body (bytes) -> [(labels, t0, float32 values)] through the library's one-pass
+    scanner (fm_parse_prometheus_matrix): no DOM, samples parsed straight into one float array."""
+    import ctypes as C
+    from ._lib import ForemastGpuError, load
+    L = load()
+    if isinstance(body, str):
+        body = body.encode()
+    ns, nv = C.c_uint32(), C.c_uint64()
+    rc = L.fm_parse_prometheus_matrix(body, len(body), None, 0, C.byref(ns), None, 0, C.byref(nv))
+    if rc not in (abi.OK, abi.E_RANGE):
+        raise ForemastGpuError(rc, "malformed Prometheus response")
+    series = np.zeros(ns.value, dtype=abi.PROM_SERIES)
+    values = np.empty(nv.value, np.float32)
+    rc = L.fm_parse_prometheus_matrix(body, len(body), series.ctypes.data, ns.value, C.byref(ns),
+                                      values.ctypes.data, nv.value, C.byref(nv))
+    if rc:
+        raise ForemastGpuError(rc, "malformed Prometheus response")
+    out = []
+    for s in series:
+        labels = json.loads(body[int(s["metric_off"]):int(s["metric_off"] + s["metric_len"])]) if s["metric_len"] else {}
+        v0 = int(s["first_value"])
+        out.append((labels, float(s["t0"]), values[v0:v0 + int(s["n_values"])]))
+    return out
+
+
 def parse_matrix(payload):
     """Prometheus query_range matrix -> [(labels, t0, float32 values)], one per result (per pod).
     Shape per foremast-dashboard/src/services/ApiService.js:36-39 / metricReducer.js:67-69:
-    data.result[].values = [[ts, "v"], ...].  Non-numeric samples become NaN (dropped at ingest)."""
+    data.result[].values = [[ts, "v"], ...].  Non-numeric samples become NaN (dropped at ingest).
+    Raw response bodies take the native scanner; already-decoded dicts are walked in Python."""
     if isinstance(payload, (str, bytes)):
-        payload = json.loads(payload)
+        return parse_matrix_native(payload)
     res = (payload or {}).get("data", {}).get("result", []) or []
     out = []
     for r in res:

@@ -217,6 +217,22 @@ void fm_host_free(fm_ctx *ctx, void *p);
 
 /* ---------------------------------------------------------------- ingest */
 
+/* Fast path from a Prometheus query_range response body (matrix) to fp32 series: the step the brain
+ * performs after fetching the URLs built by pkg/prometheus/prometheushelper.go:13-43; response shape
+ * data.result[].values[[ts,"v"],...] as read by foremast-dashboard/src/services/ApiService.js:36-39.
+ * One pass, no allocation: series[i] describes result i (byte span of its "metric" label object in
+ * `json`, first timestamp, step, and the slice values[first_value .. first_value+n_values)).
+ * With too small buffers it returns FM_E_RANGE and the required counts in n_series / n_values
+ * (call once with caps 0 to size).  Host code only. */
+typedef struct fm_prom_series {
+  uint64_t metric_off, metric_len;
+  double t0, step;
+  uint64_t first_value;
+  uint32_t n_values, reserved;
+} fm_prom_series;
+int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_prom_series *series, uint32_t series_cap,
+                               uint32_t *n_series, float *values, uint64_t values_cap, uint64_t *n_values);
+
 /* Incremental ingest of one job's series: what the brain does after fetching the three
  * query_range matrices named by currentConfig / baselineConfig / historicalConfig
  * (foremast-service/cmd/manager/main.go:50-81).  Non-finite samples are dropped (gaps),

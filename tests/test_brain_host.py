@@ -69,3 +69,35 @@ def test_reason_text_matches_trigger_regexes():
     t = re.search(r"&quot;ts&quot;\s*:\s*\[(\d*).\d", r)
     assert t and t.group(1) == "1550000060"
     assert json.loads(html.unescape(r))["anomaly"][0]["values"] == [40.134, 40.466]  # trigger.go:363 un-escapes
+
+
+def test_native_matrix_scanner_matches_json_module():
+    """fm_parse_prometheus_matrix against the json module on awkward but legal responses."""
+    rng = np.random.default_rng(3)
+    result = []
+    for i in range(7):
+        n = int(rng.integers(0, 300))
+        vals = rng.normal(1e3 ** rng.uniform(-2, 3), 5, n)
+        pts = []
+        for k, v in enumerate(vals):
+            s = repr(float(v)) if k % 5 else f"{v:.6e}"
+            if k % 41 == 40:
+                s = ["NaN", "+Inf", "-Inf"][k % 3]
+            pts.append([1550000000 + 60 * k + (0.123 if i == 3 else 0), s])
+        result.append({"metric": {"__name__": "namespace_pod_x", "pod": f"p-{i}", "weird": "a\\\"b]}[{,"}, "values": pts})
+    payload = {"status": "success", "warnings": ["x", {"y": [1, 2, {"z": "]"}]}],
+               "data": {"resultType": "matrix", "extra": [[1, "2"]], "result": result}}
+    for body in (json.dumps(payload), json.dumps(payload, indent=2), json.dumps(payload, separators=(",", ":"))):
+        got = brain.parse_matrix(body.encode())
+        want = brain.parse_matrix(json.loads(body))
+        assert len(got) == len(want) == 7
+        for (gl, gt, gv), (wl, wt, wv) in zip(got, want):
+            assert gl == wl and gt == wt
+            assert gv.tobytes() == wv.tobytes() or (np.array_equal(np.isnan(gv), np.isnan(wv)) and
+                                                    np.array_equal(gv[~np.isnan(gv)], wv[~np.isnan(wv)]))
+    assert brain.parse_matrix(b'{"status":"success","data":{"resultType":"matrix","result":[]}}') == []
+    from foremast_b200._lib import ForemastGpuError
+    import pytest
+    for bad in (b"", b"[]", b'{"data":{"result":[{"values":[[1,2]]}]}}', b'{"status":"error"}'):
+        with pytest.raises(ForemastGpuError):
+            brain.parse_matrix(bad)
