@@ -101,3 +101,15 @@ def test_native_matrix_scanner_matches_json_module():
     for bad in (b"", b"[]", b'{"data":{"result":[{"values":[[1,2]]}]}}', b'{"status":"error"}'):
         with pytest.raises(ForemastGpuError):
             brain.parse_matrix(bad)
+
+
+def test_exporter_series_names_match_dashboard():
+    """foremast-dashboard/src/config/metrics.js:20-31 names; _anomaly value = unix ts (metricReducer.js:79-80)."""
+    from foremast_b200 import exporter
+    txt = exporter.exposition("namespace_app_pod_http_server_requests_errors_5xx", "dev", "demo", upper=0.589, lower=0.0,
+                              anomaly_ts=[1550000060, 1550001260])
+    assert 'foremastbrain:namespace_app_pod_http_server_requests_errors_5xx_upper{exported_namespace="dev",app="demo"} 0.589' in txt
+    assert 'foremastbrain:namespace_app_pod_http_server_requests_errors_5xx_lower{exported_namespace="dev",app="demo"} 0.0' in txt
+    assert 'foremastbrain:namespace_app_pod_http_server_requests_errors_5xx_anomaly{exported_namespace="dev",app="demo"} 1550001260' in txt
+    assert re.match(r"^foremastbrain.*", txt.splitlines()[1])   # custom-metrics-config-map.yaml:27
+    assert exporter.exposition("m", "n", "a") == ""
