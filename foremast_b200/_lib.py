@@ -38,6 +38,9 @@ SYMBOLS = {
     "fm_batch_download": (C.c_int, [_P, _P, _P, _P, _P, _P]),
     "fm_batch_free": (None, [_P]),
     "fm_score": (C.c_int, [_P, _P, C.POINTER(abi.Params), _PP]),
+    "fm_model_fit": (C.c_int, [_P, _P, C.POINTER(abi.Params), _PP]),
+    "fm_model_score": (C.c_int, [_P, _P, _P, _PP]),
+    "fm_model_free": (None, [_P]),
     "fm_score_host": (C.c_int, [_P, C.POINTER(abi.Csr), C.POINTER(abi.Params), C.c_uint32, _P]),
     "fm_result_sync": (C.c_int, [_P]),
     "fm_result_verdicts": (C.c_int, [_P, _P, C.c_uint64, C.POINTER(C.c_uint64)]),

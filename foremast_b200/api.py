@@ -42,7 +42,7 @@ class Context:
     def close(self):
         if self._h:
             for child in sorted(self._children, key=lambda c: isinstance(c, Batch)):
-                child.free()  # results first, then batches
+                child.free()  # results and models first, then batches
             self._L.fm_shutdown(self._h)
             self._h = C.c_void_p()
 
@@ -125,6 +125,12 @@ class Context:
         self._check(self._L.fm_score(self._h, batch._h, C.byref(params), C.byref(h)))
         return Result(self, batch, h)
 
+    def model_fit(self, history_batch, params):
+        """Fit and cache the Holt-Winters state of every unit (fm_model_fit)."""
+        h = C.c_void_p()
+        self._check(self._L.fm_model_fit(self._h, history_batch._h, C.byref(params), C.byref(h)))
+        return Model(self, h)
+
     def score_host(self, csr, params, n_services=None):
         """One-shot host-in / host-out call (fm_score_host): returns VERDICT array."""
         ns = csr.n_services if n_services is None else n_services
@@ -132,6 +138,30 @@ class Context:
         st = csr.as_struct()
         self._check(self._L.fm_score_host(self._h, C.byref(st), C.byref(params), ns, out.ctypes.data))
         return out
+
+
+class Model:
+    """Cached per-unit Holt-Winters state in HBM (continuous mode): score() consumes only new samples."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self._h = ctx, handle
+        ctx._children.add(self)
+
+    def score(self, current_batch):
+        h = C.c_void_p()
+        self.ctx._check(self.ctx._L.fm_model_score(self.ctx._h, self._h, current_batch._h, C.byref(h)))
+        return Result(self.ctx, current_batch, h)
+
+    def free(self):
+        if self._h and self.ctx._h:
+            self.ctx._L.fm_model_free(self._h)
+        self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 class Batch:

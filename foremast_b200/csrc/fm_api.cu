@@ -62,7 +62,16 @@ struct fm_result {
   float *d_anom_val = nullptr;
   uint64_t anom_total = 0;
   uint32_t anom_alg = 0;
+  bool from_model = false;  // scored by fm_model_score: the batch holds no model window, so no emit pass
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // start, pre-rank, post-Wilcoxon, post-rank, post-band, post-verdict
+};
+
+struct fm_model {
+  fm_ctx *ctx = nullptr;
+  uint64_t n_units = 0;
+  fm_params params;
+  DevParams *d_params = nullptr;
+  double *d_state = nullptr;  // [n_units][period + 4]
 };
 
 namespace {
@@ -695,6 +704,84 @@ int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out
   return score_locked(ctx, b, p, out);
 }
 
+// ---- continuous-mode model cache (Holt-Winters state kept in HBM between cycles)
+
+int fm_model_fit(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_model **out) {
+  if (!ctx || !b || !p || !out) return FM_E_INVALID;
+  if (!b->sealed || b->ctx != ctx) return set_err(ctx, FM_E_STATE, "batch is not a sealed batch of this context");
+  if (p->period < 32 || p->period > 2048) return set_err(ctx, FM_E_UNSUPPORTED, "Holt-Winters period must be between 32 and 2048 samples");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  fm_model *m = new (std::nothrow) fm_model;
+  if (!m) return FM_E_NOMEM;
+  m->ctx = ctx;
+  m->n_units = b->n_units;
+  m->params = *p;
+  m->params.algorithms = FM_ALG_HW;
+  m->params.pairwise = FM_PW_NONE;
+  m->params.band_algorithm = 0;
+  cudaError_t e = cudaMalloc(&m->d_params, sizeof(DevParams));
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_state, (b->n_units * (uint64_t)(p->period + 4) + 1) * sizeof(double));
+  DevParams hp;
+  resolve_params(&m->params, &hp);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(m->d_params, &hp, sizeof(hp), cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = fm_launch_hw_fit(dev_view(b), m->d_params, p->period, m->d_state, ctx->sm_count, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(m->d_params); cudaFree(m->d_state);
+    delete m;
+    return set_err(ctx, e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA, std::string("model fit: ") + cudaGetErrorString(e));
+  }
+  *out = m;
+  return FM_OK;
+}
+
+int fm_model_score(fm_ctx *ctx, fm_model *m, const fm_batch *b, fm_result **out) {
+  if (!ctx || !m || !b || !out) return FM_E_INVALID;
+  if (!b->sealed || b->ctx != ctx || m->ctx != ctx) return set_err(ctx, FM_E_STATE, "batch / model do not belong to this context");
+  if (b->n_units != m->n_units) return set_err(ctx, FM_E_INVALID, "the current batch must hold the same units, in the same order, as the fitted one");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  fm_result *r = new (std::nothrow) fm_result;
+  if (!r) return FM_E_NOMEM;
+  int rc = result_alloc(ctx, b, &m->params, r);
+  r->from_model = true;
+  cudaStream_t st = ctx->stream;
+  cudaError_t e = cudaSuccess;
+  if (rc == FM_OK) {
+    DevBatch db = dev_view(b);
+    for (int i = 1; i <= 3 && e == cudaSuccess; ++i) e = cudaEventRecord(r->ev[i], st);
+    if (e == cudaSuccess) e = fm_launch_hw_resume(db, r->d_params, m->params.period, m->d_state, r->d_scores, r->d_unit_status,
+                                                  r->d_unit_points, ctx->sm_count, st);
+    if (e == cudaSuccess) e = cudaEventRecord(r->ev[4], st);
+    if (e == cudaSuccess) {
+      fm_launch_verdict_reduce(db, r->d_unit_status, r->d_unit_points, r->n_services, r->d_counts, r->d_worst, st);
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(r->ev[5], st);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      rc = set_err(ctx, FM_E_CUDA, std::string("model score: ") + cudaGetErrorString(e));
+    }
+  }
+  if (rc) { result_release(r); return rc; }
+  *out = r;
+  return FM_OK;
+}
+
+void fm_model_free(fm_model *m) {
+  if (!m) return;
+  {
+    std::lock_guard<std::mutex> g(m->ctx->mu);
+    cudaSetDevice(m->ctx->device);
+    cudaStreamSynchronize(m->ctx->stream);
+    cudaFree(m->d_params);
+    cudaFree(m->d_state);
+  }
+  delete m;
+}
+
 int fm_result_sync(fm_result *r) {
   if (!r) return FM_E_INVALID;
   fm_ctx *ctx = r->ctx;
@@ -765,6 +852,7 @@ int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_poin
     if (algorithm == (1u << i)) a = i;
   if (a < 0 || !(r->params.algorithms & algorithm))
     return set_err(ctx, FM_E_INVALID, "algorithm must be one FM_ALG_* bit that was enabled in fm_score");
+  if (r->from_model) return set_err(ctx, FM_E_UNSUPPORTED, "anomaly lists are not available for results of fm_model_score");
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;

@@ -85,6 +85,11 @@ cudaError_t fm_launch_band_emit(const DevBatch &b, const DevParams *dp, uint32_t
 cudaError_t fm_launch_hw_emit(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
                               const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
                               cudaStream_t st);
+cudaError_t fm_launch_hw_fit(const DevBatch &b, const DevParams *dp, uint32_t period, double *state, int sm_count,
+                             cudaStream_t st);
+cudaError_t fm_launch_hw_resume(const DevBatch &b, const DevParams *dp, uint32_t period, double *state,
+                                fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points, int sm_count,
+                                cudaStream_t st);
 uint64_t fm_scan_scratch_bytes(uint64_t n);
 cudaError_t fm_launch_scan_counts(const void *in, size_t stride, uint64_t n, unsigned long long *out,
                                   unsigned long long *scratch, cudaStream_t st);

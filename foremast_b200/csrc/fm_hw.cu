@@ -34,7 +34,11 @@ __device__ __forceinline__ V2 matvec(const double *m, V2 v) {  // m = {a00, a01,
   return r;
 }
 
-// MODE 0 score, 1 score + bands, 2 emit pass of the anomaly list (see fm_band.cu)
+// MODE 0 score, 1 score + bands, 2 emit pass of the anomaly list (see fm_band.cu),
+// MODE 3 fit: run the model window only and save (level, trend, sigma, phase, seasonals) per unit,
+// MODE 4 resume: load that state, score the current segment from it and save the advanced state --
+// the continuous-mode model cache (the brain's MAX_CACHE_SIZE, foremast-brain/README.md:30; jobs
+// re-armed every cycle with START_TIME/END_TIME, foremast-service/cmd/manager/main.go:59-63).
 template <int MODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const DevParams *__restrict__ dp,
                                                             fm_series_score *__restrict__ scores,
@@ -42,8 +46,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
                                                             uint32_t *__restrict__ unit_points,
                                                             float *__restrict__ band_up, float *__restrict__ band_lo,
                                                             const unsigned long long *__restrict__ emit_off,
-                                                            uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val) {
-  constexpr bool BANDS = MODE == 1, EMIT = MODE == 2;
+                                                            uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val,
+                                                            double *__restrict__ state) {
+  constexpr bool BANDS = MODE == 1, EMIT = MODE == 2, FIT = MODE == 3, RESUME = MODE == 4;
   extern __shared__ double s_dyn[];  // [warps][period] seasonals, then [warps][32*k] fp32 samples
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t m = dp->period, k = m / 32, lt = 32 * k;
@@ -64,42 +69,75 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
     uint32_t a0 = 0, ns = 0;
     if (nh >= dp->min_historical && nh > 0) { a0 = 0; ns = nh; }
     else if (nb >= dp->min_historical && nb > 0) { a0 = nh; ns = nb; }
-    if (ns == 0 || nc == 0 || (uint64_t)ns < 2ull * m) continue;  // unknown unit, or not two seasons of model window
+    double *const ust = (FIT || RESUME) ? state + u * (uint64_t)(m + 4) : nullptr;  // {l, b, sigma, phase | -1, S[m]}
+    if (FIT) {
+      if ((uint64_t)ns < 2ull * m) {
+        if (lane == 0) ust[3] = -1.0;  // no model for this unit
+        continue;
+      }
+    } else if (RESUME) {
+      const bool ok = nc > 0 && ust[3] >= 0.0;
+      if (!ok) {
+        if (lane == 0) {
+          fm_series_score *o = scores + u;
+#pragma unroll
+          for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
+          o->status = FM_S_UNKNOWN;
+          o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
+          unit_status[u] = FM_S_UNKNOWN;
+          unit_points[u] = 0;
+        }
+        continue;
+      }
+      ns = 0;
+    } else if (ns == 0 || nc == 0 || (uint64_t)ns < 2ull * m) {
+      continue;  // unknown unit, or not two seasons of model window
+    }
     unsigned long long emit_base = 0;
     if (EMIT) {
       emit_base = emit_off[u];
       if (emit_off[u + 1] == emit_base) continue;
     }
-    const uint32_t c0 = nh + nb, n_stream = ns + nc;
+    const uint32_t c0 = nh + nb, n_stream = FIT ? ns : ns + nc;
     const float *unit = b.values + off;
     auto sample = [&](uint32_t q) -> float { return unit[q < ns ? a0 + q : c0 + (q - ns)]; };
 
-    uint32_t st = scores[u].status;
+    uint32_t st = (FIT || RESUME) ? 0u : scores[u].status;
     const DevRule &dr = dp->rules[b.metric_type[u] < FM_MAX_METRIC_TYPES ? b.metric_type[u] : 0];
     const double kk = (st & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
     const double mlb = dr.min_lower_bound;
     const uint32_t bound = dr.bound;
 
-    // ---- initialisation from the first two seasons (D5)
-    double s0 = 0.0, s1 = 0.0;
-    for (uint32_t i = lane; i < m; i += 32) { s0 += (double)sample(i); s1 += (double)sample(m + i); }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      s0 += __shfl_xor_sync(0xffffffffu, s0, o);
-      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-    }
-    const double L0 = s0 / (double)m, M2 = s1 / (double)m;
     V2 carry;
-    carry.l = L0;
-    carry.b = (M2 - L0) / (double)m;
-    __syncwarp();
-    for (uint32_t i = lane; i < m; i += 32) S[i] = (double)sample(i) - L0;
-
     double sse = 0.0, sigma = 0.0;
     bool sigma_ready = false;
+    uint32_t phase = 0;  // seasonal slot of stream position 0
+    if (RESUME) {
+      carry.l = ust[0];
+      carry.b = ust[1];
+      sigma = ust[2];
+      sigma_ready = true;
+      phase = (uint32_t)ust[3];
+      __syncwarp();
+      for (uint32_t i = lane; i < m; i += 32) S[i] = ust[4 + i];
+    } else {
+      // ---- initialisation from the first two seasons (D5)
+      double s0 = 0.0, s1 = 0.0;
+      for (uint32_t i = lane; i < m; i += 32) { s0 += (double)sample(i); s1 += (double)sample(m + i); }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      }
+      const double L0 = s0 / (double)m, M2 = s1 / (double)m;
+      carry.l = L0;
+      carry.b = (M2 - L0) / (double)m;
+      __syncwarp();
+      for (uint32_t i = lane; i < m; i += 32) S[i] = (double)sample(i) - L0;
+    }
     uint32_t n_anom = 0, first = FM_NONE_IDX;
 
-    for (uint32_t q0 = m; q0 < n_stream; q0 += lt) {
+    for (uint32_t q0 = RESUME ? 0u : m; q0 < n_stream; q0 += lt) {
       // stage the super-tile (coalesced) and find this lane's chunk
       __syncwarp();
       {  // 4-byte async copies, all in flight together (segments are only 4 B aligned in general)
@@ -119,7 +157,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
       }
       __syncwarp();
       const uint32_t p0 = lane * k, qa = q0 + p0;           // first local / stream position of the chunk
-      const uint32_t idx0 = (qa) % m;                        // its seasonal slot
+      const uint32_t idx0 = (phase + qa) % m;                // its seasonal slot
       const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
       // seasonal slot of local sample i; chunks that cross the end of the season take the slow loops
       const bool wrap = __any_sync(0xffffffffu, idx0 + kv > m);
@@ -266,9 +304,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
           }
         }
       }
-      // next super-tile's carry: the state after lane 31's chunk (only needed while tiles are full)
-      carry.l = __shfl_sync(0xffffffffu, l, 31);
-      carry.b = __shfl_sync(0xffffffffu, bb, 31);
+      // next super-tile's carry (and the state the model cache keeps): the state after the last real
+      // sample of this super-tile, which lives in lane (nv-1)/k
+      {
+        const uint32_t nv = min(lt, n_stream - q0);
+        const int src = (int)((nv - 1) / k);
+        carry.l = __shfl_sync(0xffffffffu, l, src);
+        carry.b = __shfl_sync(0xffffffffu, bb, src);
+      }
       if (tile_has_cur) {
         const uint32_t cnt = __popcll(fmask);
         uint32_t pre = cnt;  // exclusive prefix of flag counts over lanes (chunks are in stream order)
@@ -301,8 +344,32 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
         }
       }
     }
-    if (lane == 0 && !EMIT) {
+    if (FIT || RESUME) {  // save the model: state after the last sample, residual sigma, phase, seasonals
+      if (FIT && !sigma_ready) {
+        double t = sse;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        sigma = sqrt(t / (double)(ns - m));
+      }
+      __syncwarp();
+      for (uint32_t i = lane; i < m; i += 32) ust[4 + i] = S[i];
+      if (lane == 0) {
+        ust[0] = carry.l;
+        ust[1] = carry.b;
+        ust[2] = sigma;
+        ust[3] = (double)((phase + n_stream) % m);
+      }
+      __syncwarp();
+    }
+    if (lane == 0 && !EMIT && !FIT) {
       fm_series_score *o = scores + u;
+      if (RESUME) {
+#pragma unroll
+        for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
+        o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
+        o->k_eff = kk;
+        unit_points[u] = 0;
+      }
       st |= 1u << (FM_S_ALG_SHIFT + 4);
       if (n_anom > 0 && n_anom >= dp->min_anomaly_points) st |= FM_S_ANOMALY;
       o->status = st;
@@ -321,7 +388,7 @@ template <int MODE>
 static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
                              uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                              const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
-                             cudaStream_t st) {
+                             cudaStream_t st, double *state = nullptr) {
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const uint64_t cap = (uint64_t)sm_count * 32;
   if (blocks > cap) blocks = cap;
@@ -330,7 +397,7 @@ static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t pe
   cudaError_t e = cudaFuncSetAttribute(k_hw<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_hw<MODE><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
-                                                               emit_off, emit_idx, emit_val);
+                                                               emit_off, emit_idx, emit_val, state);
   return cudaGetLastError();
 }
 
@@ -348,4 +415,17 @@ cudaError_t fm_launch_hw_emit(const DevBatch &b, const DevParams *dp, uint32_t p
                               const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
                               cudaStream_t st) {
   return launch_hw<2>(b, dp, period, scores, nullptr, nullptr, nullptr, nullptr, emit_off, emit_idx, emit_val, sm_count, st);
+}
+
+// Continuous-mode model cache: fit = model window only, state saved; resume = score the current
+// segment from the saved state and advance it.  state holds (period + 4) doubles per unit.
+cudaError_t fm_launch_hw_fit(const DevBatch &b, const DevParams *dp, uint32_t period, double *state, int sm_count,
+                             cudaStream_t st) {
+  return launch_hw<3>(b, dp, period, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sm_count, st, state);
+}
+
+cudaError_t fm_launch_hw_resume(const DevBatch &b, const DevParams *dp, uint32_t period, double *state,
+                                fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points, int sm_count,
+                                cudaStream_t st) {
+  return launch_hw<4>(b, dp, period, scores, unit_status, unit_points, nullptr, nullptr, nullptr, nullptr, nullptr, sm_count, st, state);
 }

@@ -193,6 +193,7 @@ typedef struct fm_config {
 typedef struct fm_ctx fm_ctx;
 typedef struct fm_batch fm_batch;
 typedef struct fm_result fm_result;
+typedef struct fm_model fm_model;
 
 /* ---------------------------------------------------------------- life cycle */
 
@@ -277,6 +278,19 @@ int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_serie
 /* upper/lower band of the current segment of one unit, for the foremastbrain:*_upper/_lower
  * gauges (foremast-dashboard/src/config/metrics.js:20-31).  Needs params.band_algorithm. */
 int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uint32_t cap, uint32_t *n);
+/* Continuous-mode model cache: the brain keeps fitted models between cycles
+ * (MAX_CACHE_SIZE, foremast-brain/README.md:30) while continuous / hpa jobs are re-armed with fresh
+ * START_TIME / END_TIME every cycle (foremast-service/cmd/manager/main.go:59-63;
+ * foremast-barrelman/pkg/controller/Barrelman.go:552-565).  fm_model_fit runs Holt-Winters over the
+ * model window of every unit once and keeps (level, trend, residual sigma, phase, seasonals) in
+ * HBM -- (period + 4) doubles per unit.  fm_model_score then scores a batch that carries only the
+ * NEW current samples of the same units, in the same order, from that state, and advances the
+ * state, so each cycle costs the new window, not the 7-day history.  sigma stays the one of the
+ * fit.  Units whose model window was shorter than two periods are `unknown`. */
+int fm_model_fit(fm_ctx *ctx, const fm_batch *history, const fm_params *p, fm_model **out);
+int fm_model_score(fm_ctx *ctx, fm_model *m, const fm_batch *current, fm_result **out);
+void fm_model_free(fm_model *m);
+
 /* Compact list of the anomalous current points of ONE algorithm, the device-side form of the
  * anomaly pairs barrelman decodes as [t0, v0, t1, v1, ...]
  * (foremast-barrelman/pkg/controller/DeploymentController.go:443-452; t = current start + idx*step).

@@ -180,6 +180,48 @@ def test_holt_winters(ctx, oracle, shape, period, n):
     b.free()
 
 
+@pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400)])
+def test_model_cache_continuous_mode(ctx, oracle, period, hist):
+    """Continuous mode: fit Holt-Winters once, then score successive current windows from the cached
+    state.  Must equal one oracle pass over history + all windows (sigma is the fit's)."""
+    n, c1, c2 = 300, 37, 70
+    full = oracle.synth(n, hist, 0, c1 + c2, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=period, units_per_service=6)
+    units = [full.segments(u) for u in range(n)]
+    p = full_params(oracle, abi.ALG_HW, abi.PW_NONE)
+    p.period = period
+    k1 = [min(c1, len(c)) for _, _, c in units]
+    ref1 = oracle.score(abi.HostCsr.from_units([(h, [], c[:k]) for (h, _, c), k in zip(units, k1)], full.service_id, full.metric_type), p)[0]
+    ref12 = oracle.score(full, p)[0]
+    hb = ctx.batch_from_units([(h, [], []) for h, _, _ in units], full.service_id, full.metric_type)
+    b1 = ctx.batch_from_units([([], [], c[:k]) for (_, _, c), k in zip(units, k1)], full.service_id, full.metric_type)
+    b2 = ctx.batch_from_units([([], [], c[k:]) for (_, _, c), k in zip(units, k1)], full.service_id, full.metric_type)
+    model = ctx.model_fit(hb, p)
+    r1 = model.score(b1)
+    g1 = r1.series()
+    r2 = model.score(b2)
+    g2 = r2.series()
+    fitted = (ref12["status"] >> (abi.S_ALG_SHIFT + 4)) & 1
+    assert fitted.mean() > 0.9
+    ok1 = (fitted == 1) & (np.array(k1) > 0)
+    assert np.array_equal(g1["n_anom"][ok1, 4], ref1["n_anom"][ok1, 4])
+    assert np.array_equal(g1["first_idx"][ok1, 4], ref1["first_idx"][ok1, 4])
+    np.testing.assert_allclose(g1["sigma"][ok1, 4], ref12["sigma"][ok1, 4], rtol=REL_TOL)
+    n2 = np.array([len(c) - k for (_, _, c), k in zip(units, k1)])
+    ok2 = (fitted == 1) & (n2 > 0)
+    assert np.array_equal(g2["n_anom"][ok2, 4], (ref12["n_anom"][:, 4] - ref1["n_anom"][:, 4])[ok2])
+    # units without two seasons of history (or without new samples) are unknown, the rest carry the HW bit
+    assert np.all(g1["status"][fitted == 0] & abi.S_UNKNOWN) and np.all(g2["status"][n2 == 0] & abi.S_UNKNOWN)
+    assert np.all((g2["status"][ok2] >> (abi.S_ALG_SHIFT + 4)) & 1)
+    v = r2.verdicts()
+    assert int(v["n_units"].sum()) == n and int(v["n_anom_units"].sum()) == int(((g2["status"] & abi.S_ANOMALY) != 0).sum())
+    assert (g2["n_anom"][:, 4] > 0).any()
+    from foremast_b200._lib import ForemastGpuError
+    with pytest.raises(ForemastGpuError):
+        r2.anomalies(abi.ALG_HW)
+    for o in (r1, r2, model, hb, b1, b2):
+        o.free()
+
+
 def test_edge_cases(ctx, oracle):
     rng = np.random.default_rng(11)
     z = rng.normal(10, 1, 200).astype(np.float32)
