@@ -24,6 +24,7 @@ constexpr int kStages = 2;        // current chunk + one in flight (deeper rings
 constexpr int kWarpsPerBlock = 8;
 constexpr int kRingBytes = kWarpsPerBlock * kStages * 32 * kRowWords * 4;
 constexpr int kSmemBytes = kRingBytes + kWarpsPerBlock * 32 * (8 + 4);
+constexpr int kLoBytes = kWarpsPerBlock * 32 * kRowWords * 4;  // MODE 1: staging of the lower band, one chunk per warp
 
 struct Rule {
   double k, mlb;
@@ -227,6 +228,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kStages * 32 * kRowWords);
   int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingBytes) + warp * 32;
   uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingBytes + kWarpsPerBlock * 32 * 8) + warp * 32;
+  float *const s_lo = reinterpret_cast<float *>(smem_raw + kSmemBytes) + warp * (32 * kRowWords);  // MODE 1 only
   const uint64_t u = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * 32 + lane;
   const bool have = u < b.n_units;
 
@@ -330,6 +332,37 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
         src_update<ALGS>(s, (double)x.y, alpha, ab, q + 1, lag, cls_src);
         src_update<ALGS>(s, (double)x.z, alpha, ab, q + 2, lag, cls_src);
         src_update<ALGS>(s, (double)x.w, alpha, ab, q + 3, lag, cls_src);
+      }
+    } else if (MODE == 1 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
+      // Band materialisation: each lane writes its 32 upper values over the samples it has just
+      // consumed (same smem row) and its 32 lower values into a second tile; then the warp stores
+      // both tiles with the mirror image of the staging pattern -- 8 lanes x 16 B per unit row --
+      // so the band arrays are written in full 128 B lines instead of 4 B at a 5.7 KB stride.
+      float *uprow = s_ring + (ch % kStages) * (32 * kRowWords) + lane * kRowWords;
+      float *lorow = s_lo + lane * kRowWords;
+#pragma unroll
+      for (int v4 = 0; v4 < 8; ++v4) {
+        const float4 x = *reinterpret_cast<const float4 *>(uprow + v4 * 4);
+        const uint32_t j = cs + v4 * 4 - c0;
+        float4 bu, bl;
+        cur_update<ALGS>(s, r, (double)x.x, j + 0, cls_cur, alpha, ab, bu.x, bl.x, band_alg, lag);
+        cur_update<ALGS>(s, r, (double)x.y, j + 1, cls_cur, alpha, ab, bu.y, bl.y, band_alg, lag);
+        cur_update<ALGS>(s, r, (double)x.z, j + 2, cls_cur, alpha, ab, bu.z, bl.z, band_alg, lag);
+        cur_update<ALGS>(s, r, (double)x.w, j + 3, cls_cur, alpha, ab, bu.w, bl.w, band_alg, lag);
+        *reinterpret_cast<float4 *>(uprow + v4 * 4) = bu;
+        *reinterpret_cast<float4 *>(lorow + v4 * 4) = bl;
+      }
+      const unsigned rows_ok = __ballot_sync(0xffffffffu, cls_cur);
+      __syncwarp();
+      const float *ups = s_ring + (ch % kStages) * (32 * kRowWords);
+#pragma unroll
+      for (int rr = 0; rr < 8; ++rr) {
+        const unsigned rw = rr * 4 + row_sub;
+        if ((rows_ok >> rw) & 1u) {
+          const int64_t at = s_off[rw] + cs + col4 * 4;  // unit start and chunk start are multiples of 4: 16 B aligned
+          *reinterpret_cast<float4 *>(band_up + at) = *reinterpret_cast<const float4 *>(ups + rw * kRowWords + col4 * 4);
+          *reinterpret_cast<float4 *>(band_lo + at) = *reinterpret_cast<const float4 *>(s_lo + rw * kRowWords + col4 * 4);
+        }
       }
     } else if (MODE == 0 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
       uint32_t mask[4] = {0u, 0u, 0u, 0u};
@@ -435,9 +468,10 @@ cudaError_t launch_mode(const DevBatch &b, const DevParams *dp, bool rank_ran, f
   const uint64_t per_block = kWarpsPerBlock * 32;
   const unsigned grid = (unsigned)((b.n_units + per_block - 1) / per_block);
   if (grid == 0) return cudaSuccess;
-  cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  constexpr int smem = kSmemBytes + (MODE == 1 ? kLoBytes : 0);
+  cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  k_band<ALGS, MODE><<<grid, kWarpsPerBlock * 32, kSmemBytes, st>>>(b, dp, rank_ran, scores, unit_status, unit_points,
+  k_band<ALGS, MODE><<<grid, kWarpsPerBlock * 32, smem, st>>>(b, dp, rank_ran, scores, unit_status, unit_points,
                                                                     band_up, band_lo, emit_off, emit_idx, emit_val);
   return cudaGetLastError();
 }
