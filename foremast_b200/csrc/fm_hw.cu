@@ -254,8 +254,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
             double lo1 = fma(-kk, sigma, f1), lo2 = fma(-kk, sigma, f2);
             lo1 = lo1 < mlb ? mlb : lo1;
             lo2 = lo2 < mlb ? mlb : lo2;
-            if (((bound & 1u) && x1 > up1) || ((bound & 2u) && x1 < lo1)) fmask |= 1ull << ii;
-            if (((bound & 1u) && x2 > up2) || ((bound & 2u) && x2 < lo2)) fmask |= 2ull << ii;
+            // guarded comparison (DECISIONS "HW"): excursions below 1e-9 relative do not count
+            const double g1x = 1e-9 * (fabs(f1) + fabs(x1)), g2x = 1e-9 * (fabs(f2) + fabs(x2));
+            if (((bound & 1u) && x1 - up1 > g1x) || ((bound & 2u) && lo1 - x1 > g1x)) fmask |= 1ull << ii;
+            if (((bound & 1u) && x2 - up2 > g2x) || ((bound & 2u) && lo2 - x2 > g2x)) fmask |= 2ull << ii;
             if (BANDS) {
               const int64_t at = off + c0 + (qa + ii - ns);
               band_up[at] = (float)up1; band_lo[at] = (float)lo1;
@@ -286,7 +288,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
             const double up = fma(kk, sigma, f);
             double lo = fma(-kk, sigma, f);
             lo = lo < mlb ? mlb : lo;
-            if (((bound & 1u) && x > up) || ((bound & 2u) && x < lo)) fmask |= 1ull << i;
+            const double gx = 1e-9 * (fabs(f) + fabs(x));
+            if (((bound & 1u) && x - up > gx) || ((bound & 2u) && lo - x > gx)) fmask |= 1ull << i;
             if (BANDS) {
               band_up[off + c0 + (qa + i - ns)] = (float)up;
               band_lo[off + c0 + (qa + i - ns)] = (float)lo;

@@ -388,7 +388,10 @@ static int score_unit(const fm_params *p, const float *hist, uint32_t nh, const 
     for (uint32_t j = 0; j < nc; ++j) {
       double x = (double)cur[j], lb = l + b, f = lb + sc->S[idx], up, lo;
       band(f, sigma, &r, &up, &lo);
-      if (outside(x, up, lo, r.bound)) note(o, 4, j);
+      /* guarded comparison (DECISIONS "HW"): excursions below 1e-9 relative do not count, so that an
+       * implementation that re-associates the recurrence (the CUDA scan) flags the same points */
+      double guard = 1e-9 * (fabs(f) + fabs(x));
+      if (((r.bound & 1u) && x - up > guard) || ((r.bound & 2u) && lo - x > guard)) note(o, 4, j);
       if (want_band_alg == FM_ALG_HW) { bu[j] = (float)up; bl[j] = (float)lo; }
       double e = x - f;
       l = fma(p->alpha, e, lb);
