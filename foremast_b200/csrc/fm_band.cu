@@ -22,6 +22,10 @@ constexpr int kChunk = 32;        // samples per row per stage
 constexpr int kRowWords = 36;     // 32 + 4 pad words: 16 B aligned rows, conflict-free LDS.128
 constexpr int kStages = 2;        // current chunk + one in flight (deeper rings cost occupancy: 3 -> 2 gained 12 %)
 constexpr int kWarpsPerBlock = 8;
+// Variants with the rolling band keep one more slot: the chunk BEFORE the current one stays intact,
+// so the lagging sample (W <= 32 back) comes from shared memory instead of a scattered global load.
+__host__ __device__ constexpr int ring_slots(uint32_t algs) { return (algs & FM_ALG_MA_ROLLING) ? kStages + 1 : kStages; }
+__host__ __device__ constexpr int ring_bytes(uint32_t algs) { return kWarpsPerBlock * ring_slots(algs) * 32 * kRowWords * 4; }
 constexpr int kRingBytes = kWarpsPerBlock * kStages * 32 * kRowWords * 4;
 constexpr int kSmemBytes = kRingBytes + kWarpsPerBlock * 32 * (8 + 4);
 constexpr int kLoBytes = kWarpsPerBlock * 32 * kRowWords * 4;  // MODE 1: staging of the lower band, one chunk per warp
@@ -48,15 +52,21 @@ struct State {
 };
 
 // One sample of the stream W positions back, for the lagging prefix sums of the rolling band.
-// Read straight from global memory: the line was fetched by the main stream moments ago and sits
-// in L1/L2, so this costs no HBM traffic.
+// If it lies in the current or the previous 32-sample chunk it is still in this lane's row of the
+// shared-memory ring (4-way bank conflict at worst); otherwise it is read from global memory, where
+// the main stream fetched the line moments ago (L1/L2 hit, no HBM traffic, but 32 different lines
+// per warp instruction -- 6x slower, measured, when every sample went that way).
 struct Lag {
   const float *unit;   // values + offset of this unit
+  const float *srow;   // this lane's row in ring slot 0
   uint32_t a0, ns, c0, W;
+  uint32_t lo_pos, cur_chunk, cur_off, prev_off;  // smem holds unit positions >= lo_pos; slot offsets in floats
   __device__ __forceinline__ bool at(uint32_t q, double &x) const {
     if (q < W) return false;
     const uint32_t sp = q - W;
-    x = (double)__ldg(unit + (sp < ns ? a0 + sp : c0 + (sp - ns)));
+    const uint32_t p = sp < ns ? a0 + sp : c0 + (sp - ns);
+    if (p >= lo_pos) x = (double)srow[((p >> 5) == cur_chunk ? cur_off : prev_off) + (p & 31u)];
+    else x = (double)__ldg(unit + p);
     return true;
   }
 };
@@ -225,10 +235,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   constexpr int kSlot = (ALGS & FM_ALG_MA_ALL) ? 0 : (ALGS & FM_ALG_EWMA) ? 1 : (ALGS & FM_ALG_DES) ? 2 : 3;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
-  float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kStages * 32 * kRowWords);
-  int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingBytes) + warp * 32;
-  uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingBytes + kWarpsPerBlock * 32 * 8) + warp * 32;
-  float *const s_lo = reinterpret_cast<float *>(smem_raw + kSmemBytes) + warp * (32 * kRowWords);  // MODE 1 only
+  constexpr int kSlots = ring_slots(ALGS);
+  constexpr int kRingB = ring_bytes(ALGS);
+  float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kSlots * 32 * kRowWords);
+  int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingB) + warp * 32;
+  uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingB + kWarpsPerBlock * 32 * 8) + warp * 32;
+  float *const s_lo = reinterpret_cast<float *>(smem_raw + kRingB + kWarpsPerBlock * 32 * (8 + 4)) + warp * (32 * kRowWords);  // MODE 1 only
   const uint64_t u = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * 32 + lane;
   const bool have = u < b.n_units;
 
@@ -281,6 +293,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   for (int a = 0; a < 4; ++a) { s.cnt[a] = 0; s.first[a] = FM_NONE_IDX; }
   Lag lag;
   lag.unit = b.values + off;
+  lag.srow = s_ring + lane * kRowWords;
+  lag.lo_pos = 0xFFFFFFFFu; lag.cur_chunk = 0; lag.cur_off = 0; lag.prev_off = 0;
   lag.a0 = a0; lag.ns = ns; lag.c0 = c0;
   lag.W = active ? dp->ma_window : 0xFFFFFFFFu;  // lanes without a unit never touch memory
 
@@ -294,7 +308,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
 
   auto issue = [&](uint32_t ch) {
     if (ch < nchunks) {
-      float *dst = s_ring + (ch % kStages) * (32 * kRowWords);
+      float *dst = s_ring + (ch % kSlots) * (32 * kRowWords);
 #pragma unroll
       for (int rr = 0; rr < 8; ++rr) {
         const unsigned row = rr * 4 + row_sub;
@@ -314,7 +328,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     __syncwarp();
     issue(ch + kStages - 1);
 
-    const float *row = s_ring + (ch % kStages) * (32 * kRowWords) + lane * kRowWords;
+    const float *row = s_ring + (ch % kSlots) * (32 * kRowWords) + lane * kRowWords;
+    if (ALGS & FM_ALG_MA_ROLLING) {
+      lag.cur_chunk = ch;
+      lag.cur_off = (ch % kSlots) * (32 * kRowWords);
+      lag.prev_off = ((ch + kSlots - 1) % kSlots) * (32 * kRowWords);
+      lag.lo_pos = ch ? (ch - 1) * kChunk : 0u;
+    }
     const uint32_t cs = ch * kChunk, ce = cs + kChunk;
     const bool done = cs >= c1, not_started = ce <= a0;
     const bool cls_src = cs >= a0 + 2 && ce <= a1;
@@ -338,7 +358,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       // consumed (same smem row) and its 32 lower values into a second tile; then the warp stores
       // both tiles with the mirror image of the staging pattern -- 8 lanes x 16 B per unit row --
       // so the band arrays are written in full 128 B lines instead of 4 B at a 5.7 KB stride.
-      float *uprow = s_ring + (ch % kStages) * (32 * kRowWords) + lane * kRowWords;
+      float *uprow = s_ring + (ch % kSlots) * (32 * kRowWords) + lane * kRowWords;
       float *lorow = s_lo + lane * kRowWords;
 #pragma unroll
       for (int v4 = 0; v4 < 8; ++v4) {
@@ -354,7 +374,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       }
       const unsigned rows_ok = __ballot_sync(0xffffffffu, cls_cur);
       __syncwarp();
-      const float *ups = s_ring + (ch % kStages) * (32 * kRowWords);
+      const float *ups = s_ring + (ch % kSlots) * (32 * kRowWords);
 #pragma unroll
       for (int rr = 0; rr < 8; ++rr) {
         const unsigned rw = rr * 4 + row_sub;
@@ -468,7 +488,7 @@ cudaError_t launch_mode(const DevBatch &b, const DevParams *dp, bool rank_ran, f
   const uint64_t per_block = kWarpsPerBlock * 32;
   const unsigned grid = (unsigned)((b.n_units + per_block - 1) / per_block);
   if (grid == 0) return cudaSuccess;
-  constexpr int smem = kSmemBytes + (MODE == 1 ? kLoBytes : 0);
+  constexpr int smem = ring_bytes(ALGS) + kWarpsPerBlock * 32 * (8 + 4) + (MODE == 1 ? kLoBytes : 0);
   cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_band<ALGS, MODE><<<grid, kWarpsPerBlock * 32, smem, st>>>(b, dp, rank_ran, scores, unit_status, unit_points,
