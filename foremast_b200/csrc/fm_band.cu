@@ -26,8 +26,6 @@ constexpr int kWarpsPerBlock = 8;
 // so the lagging sample (W <= 32 back) comes from shared memory instead of a scattered global load.
 __host__ __device__ constexpr int ring_slots(uint32_t algs) { return (algs & FM_ALG_MA_ROLLING) ? kStages + 1 : kStages; }
 __host__ __device__ constexpr int ring_bytes(uint32_t algs) { return kWarpsPerBlock * ring_slots(algs) * 32 * kRowWords * 4; }
-constexpr int kRingBytes = kWarpsPerBlock * kStages * 32 * kRowWords * 4;
-constexpr int kSmemBytes = kRingBytes + kWarpsPerBlock * 32 * (8 + 4);
 constexpr int kLoBytes = kWarpsPerBlock * 32 * kRowWords * 4;  // MODE 1: staging of the lower band, one chunk per warp
 
 struct Rule {

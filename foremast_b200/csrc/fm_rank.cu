@@ -24,7 +24,7 @@
 
 namespace {
 
-constexpr int kWarpsPerBlock = 4;
+constexpr int kWarpsPerBlock = 8;
 constexpr uint32_t kKeySentinel = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint32_t sel_minmax(bool lower, uint32_t a, uint32_t b) { return lower ? min(a, b) : max(a, b); }
@@ -209,7 +209,7 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
 // lost 4-5 issue slots per issued instruction to fetch stalls), and both are ALU-bound, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
 template <int R, int PHASE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 3 : 6) k_rank(DevBatch b, const DevParams *__restrict__ dp,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(DevBatch b, const DevParams *__restrict__ dp,
                                                               fm_series_score *__restrict__ scores, const int tile_words,
                                                               const int kRl) {
   // PHASE 0 keeps the compile-time tile (one tile per warp is small anyway; a run-time size cost it
