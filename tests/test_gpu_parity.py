@@ -260,6 +260,26 @@ def test_edge_cases(ctx, oracle):
     e.free()
 
 
+def test_size_limits(ctx, oracle):
+    """Longest inputs: a 50 000-sample history streams through the band kernel; rank segments above
+    2048 samples are refused with FM_E_UNSUPPORTED (and scored fine once the rank tests are off)."""
+    from foremast_b200._lib import ForemastGpuError
+    rng = np.random.default_rng(2)
+    z = rng.normal(50, 3, 60000).astype(np.float32)
+    b = ctx.batch_from_units([(z[:50000], z[50000:52048], z[52048:54096]), (z[:37], z[100:140], z[200:260])],
+                             service_id=[0, 0], metric_type=[abi.MT_CPU, abi.MT_LATENCY])
+    p = full_params(oracle)
+    check_batch(ctx, oracle, b, p)
+    b.free()
+    big = ctx.batch_from_units([(z[:100], z[100:2200], z[3000:3100])])
+    with pytest.raises(ForemastGpuError) as ei:
+        ctx.score(big, p)
+    assert ei.value.code == abi.E_UNSUPPORTED
+    p.pairwise = abi.PW_NONE
+    check_batch(ctx, oracle, big, p)
+    big.free()
+
+
 def test_bulk_csr_ingest_and_realignment(ctx, oracle):
     h = oracle.synth(300, 50, 21, 22, flags=abi.SYNTH_ANOMALIES)
     p = full_params(oracle)
