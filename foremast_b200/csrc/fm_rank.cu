@@ -18,6 +18,7 @@
 // aligned in general, and this kernel is issue-bound on the sort, not on HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
 #include <algorithm>
+#include <utility>
 
 #include "fm_common.cuh"
 #include "fm_rank_merge.h"
@@ -36,46 +37,94 @@ __device__ __forceinline__ uint32_t float_key(float x) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// Ascending bitonic sort of 32*R u32 keys held as v[r] = element lane*R + r.  Every merge starts
-// with a "mirror" step (partner = e ^ (k-1)) so all compare-exchanges point the same way and no
-// direction flags are needed.  Phase 1 sorts the R keys of each lane in registers; phase 2 runs
-// the five cross-lane merges as a ROLLED loop (lane masks are runtime values, register indices
-// stay static) so the whole sort is ~1k instructions and stays in the instruction cache -- the
-// fully unrolled network (12k instructions per kernel) stalled 7 of 8 issue slots on fetch.
+// ---- register-resident sort of 32*R u32 keys, R = 2^q or 3*2^q ---------------------------------
+// Lane `lane` holds v[r] = element lane*R + r.  Three pieces:
+//  1. lane_sort: the R keys of each lane, by Batcher's merge-exchange network generated at compile
+//     time for exactly R inputs (132 comparators for R = 24, 191 for R = 32);
+//  2. five cross-lane merges (2, 4, .. 32 lanes) as a ROLLED loop: a "mirror" step (partner element
+//     2L-1-e, so every compare-exchange points the same way and no direction flags are needed)
+//     followed by half-cleaners over lane bits -- lane masks are runtime values, register indices
+//     stay static, so the whole sort is ~1k instructions and stays in the instruction cache (the
+//     fully unrolled network, 12k instructions per kernel, stalled 7 of 8 issue slots on fetch);
+//  3. lane_bitonic_merge: each lane's R registers are then a bitonic sequence; half-cleaners while
+//     the length is even (valid for any even length), and a 3-sorter per group when R = 3*2^q.
+// R = 3*2^q exists because the sort is the kernel's cost and it is paid per SLOT, not per sample:
+// 720-sample segments in a 1024-slot network waste 30 % of it, in a 768-slot one 6 %.
 template <int R>
-__device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsigned lane) {
+struct LaneNet {
+  int n = 0;
+  unsigned char a[R * 9 + 1] = {}, b[R * 9 + 1] = {};
+};
+
+template <int R>
+__host__ __device__ constexpr LaneNet<R> make_lane_net() {
+  LaneNet<R> t{};
+  for (int p = 1; p < R; p *= 2)
+    for (int k = p; k >= 1; k /= 2)
+      for (int j = k % p; j <= R - 1 - k; j += 2 * k)
+        for (int i = 0; i <= (k - 1 < R - j - k - 1 ? k - 1 : R - j - k - 1); ++i)
+          if ((i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+            t.a[t.n] = (unsigned char)(i + j);
+            t.b[t.n] = (unsigned char)(i + j + k);
+            ++t.n;
+          }
+  return t;
+}
+
+template <int R, int... I>
+__device__ __forceinline__ void lane_sort_impl(uint32_t (&v)[R], std::integer_sequence<int, I...>) {
+  constexpr LaneNet<R> net = make_lane_net<R>();
+  (cex(v[net.a[I]], v[net.b[I]]), ...);
+}
+
+template <int R>
+__device__ __forceinline__ void lane_sort(uint32_t (&v)[R]) {
+  constexpr int n = make_lane_net<R>().n;
+  if constexpr (n > 0) lane_sort_impl<R>(v, std::make_integer_sequence<int, n>{});
+}
+
+__host__ __device__ constexpr int odd_part(int r) { return (r & 1) ? r : odd_part(r >> 1); }
+__host__ __device__ constexpr int halvings(int r) { return (r & 1) ? 0 : 1 + halvings(r >> 1); }
+
+template <int R>
+__device__ __forceinline__ void lane_bitonic_merge(uint32_t (&v)[R]) {
+  constexpr int kHalvings = halvings(R);
 #pragma unroll
-  for (int k = 2; k <= R; k <<= 1) {
+  for (int s = 0; s < kHalvings; ++s) {
+    const int len = R >> s, half = len >> 1;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const int pr = r ^ (k - 1);
-      if (pr > r) cex(v[r], v[pr]);
-    }
+    for (int r = 0; r < R; ++r)
+      if (r % len < half) cex(v[r], v[r + half]);
+  }
+  if constexpr (odd_part(R) == 3) {
 #pragma unroll
-    for (int j = k >> 2; j >= 1; j >>= 1) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int pr = r ^ j;
-        if (pr > r) cex(v[r], v[pr]);
-      }
+    for (int g = 0; g < R; g += 3) {
+      cex(v[g], v[g + 1]);
+      cex(v[g + 1], v[g + 2]);
+      cex(v[g], v[g + 1]);
     }
   }
+}
+
+template <int R>
+__device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsigned lane) {
+  static_assert(odd_part(R) == 1 || odd_part(R) == 3, "R must be 2^q or 3*2^q");
+  lane_sort<R>(v);
 #pragma unroll 1
-  for (unsigned kk = 1; kk <= 16; kk <<= 1) {  // merge size k = 2*R*kk
+  for (unsigned kk = 1; kk <= 16; kk <<= 1) {  // merges 2*kk lanes, L = R*kk elements a side
     {
       const unsigned lm = 2 * kk - 1;
       const bool lower = (lane & kk) == 0;
-      if (R == 1) {
-        const uint32_t a = __shfl_xor_sync(0xffffffffu, v[0], lm);
-        v[0] = sel_minmax(lower, v[0], a);
-      } else {
 #pragma unroll
-        for (int r = 0; r < R / 2; ++r) {
-          const uint32_t a = __shfl_xor_sync(0xffffffffu, v[R - 1 - r], lm);
-          const uint32_t c = __shfl_xor_sync(0xffffffffu, v[r], lm);
-          v[r] = sel_minmax(lower, v[r], a);
-          v[R - 1 - r] = sel_minmax(lower, v[R - 1 - r], c);
-        }
+      for (int r = 0; r < R / 2; ++r) {
+        const uint32_t a = __shfl_xor_sync(0xffffffffu, v[R - 1 - r], lm);
+        const uint32_t c = __shfl_xor_sync(0xffffffffu, v[r], lm);
+        v[r] = sel_minmax(lower, v[r], a);
+        v[R - 1 - r] = sel_minmax(lower, v[R - 1 - r], c);
+      }
+      if constexpr (R & 1) {  // the middle register mirrors onto itself
+        const uint32_t a = __shfl_xor_sync(0xffffffffu, v[R / 2], lm);
+        v[R / 2] = sel_minmax(lower, v[R / 2], a);
       }
     }
 #pragma unroll 1
@@ -87,14 +136,7 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsign
         v[r] = sel_minmax(lower, v[r], a);
       }
     }
-#pragma unroll
-    for (int j = R >> 1; j >= 1; j >>= 1) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int pr = r ^ j;
-        if (pr > r) cex(v[r], v[pr]);
-      }
-    }
+    lane_bitonic_merge<R>(v);
   }
 }
 
@@ -316,11 +358,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
       } else {
         const float *src = seg == 1 ? base : cur;
         n_valid = seg == 1 ? nb : nc;
+        // unconditional loads from a clamped index: predicated ones get serialised two at a time
+        // (one predicate register each), which exposed a dozen L2 round trips per segment
+        const uint32_t last = n_valid - 1;  // pooled implies n_valid > 0
+        float x[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const uint32_t e = r * 32 + lane;
-          key[r] = e < n_valid ? float_key(src[e]) : kKeySentinel;
-        }
+        for (int r = 0; r < R; ++r) x[r] = __ldg(src + min((uint32_t)(r * 32) + lane, last));
+#pragma unroll
+        for (int r = 0; r < R; ++r) key[r] = (uint32_t)(r * 32) + lane < n_valid ? float_key(x[r]) : kKeySentinel;
       }
       warp_bitonic_sort<R>(key, lane);
 
@@ -465,10 +510,15 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
   if (max_seg <= 32) return launch<1>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 64) return launch<2>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 96) return launch<3>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 128) return launch<4>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 192) return launch<6>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 384) return launch<12>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 768) return launch<24>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
+  if (max_seg <= 1536) return launch<48>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   if (max_seg <= 2048) return launch<64>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
   return cudaErrorInvalidValue;
 }

@@ -135,6 +135,36 @@ def test_score_parity_on_synthetic_batches(ctx, oracle, shape, n):
     b.free()
 
 
+@pytest.mark.parametrize("longest", [3, 32, 33, 64, 65, 96, 97, 128, 150, 192, 193, 256, 300, 384, 385, 512, 600, 720,
+                                     768, 769, 1024, 1025, 1536, 1537, 2048])
+def test_rank_sort_size_classes(ctx, oracle, longest):
+    """The rank kernels sort in 32*R register slots, R = 2^q or 3*2^q chosen from the longest
+    segment of the batch: one batch per class boundary, ragged lengths below it, with ties (values
+    rounded to a coarse grid), without, and all-equal / reversed runs."""
+    rng = np.random.default_rng(longest)
+    units = []
+    for i in range(40):
+        nb = longest if i < 2 else int(rng.integers(max(1, longest // 2), longest + 1))
+        nc = longest if i in (0, 3) else int(rng.integers(max(1, longest // 2), longest + 1))
+        base = rng.normal(100, 10, nb)
+        cur = rng.normal(100 + (i % 3), 10, nc)
+        if i % 4 == 1:
+            base, cur = np.round(base), np.round(cur)            # many ties, across and inside groups
+        elif i % 4 == 2:
+            base, cur = np.round(base / 8) * 8, np.round(cur / 8) * 8  # long runs
+        elif i == 7:
+            base[:] = 5.0
+            cur[:] = 5.0
+        elif i == 11:
+            base, cur = np.sort(base)[::-1].copy(), np.sort(cur)
+        units.append((rng.normal(100, 10, 40), base, cur))
+    b = ctx.batch_from_units(units, service_id=[i // 10 for i in range(40)], metric_type=[i % 8 for i in range(40)])
+    p = full_params(oracle, algs=abi.ALG_MA_ALL)
+    p.min_mann_white = p.min_wilcoxon = p.min_kruskal = 1
+    check_batch(ctx, oracle, b, p)
+    b.free()
+
+
 @pytest.mark.parametrize("pairwise", [abi.PW_NONE, abi.PW_ANY, abi.PW_MANN_WHITE, abi.PW_WILCOXON, abi.PW_KRUSKAL])
 @pytest.mark.parametrize("algs", [abi.ALG_MA_ALL, abi.ALG_EWMA, abi.ALG_DES, abi.ALG_MA_ALL | abi.ALG_DES,
                                   abi.ALG_MA_ROLLING, abi.ALG_MA_ROLLING | abi.ALG_EWMA])
