@@ -371,12 +371,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
 
       // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1)
       const uint32_t sh = PHASE == 0 ? 1u : 0u;  // |d| keys carry the sign in bit 0
+      // slots of this lane that hold real samples (compared against literals below: a bound written
+      // as lane*R + r < n_valid gets hoisted into R loop-invariant registers, and those spilled)
+      const int rem = (int)n_valid - (int)(lane * R);
       bool tie = false;
 #pragma unroll
-      for (int r = 0; r + 1 < R; ++r)
-        tie = tie || (((key[r] >> sh) == (key[r + 1] >> sh)) && (lane * R + r + 1 < n_valid));
+      for (int r = 0; r + 1 < R; ++r) tie = tie || (((key[r] >> sh) == (key[r + 1] >> sh)) && (r + 1 < rem));
       const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1);
-      tie = tie || (lane < 31 && ((key[R - 1] >> sh) == (nxt >> sh)) && (lane * R + R < n_valid));
+      tie = tie || (lane < 31 && ((key[R - 1] >> sh) == (nxt >> sh)) && (R < rem));
       const bool any_tie = __any_sync(0xffffffffu, tie);
 
       if (PHASE == 0) {
@@ -385,15 +387,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
           // tie-free |d|: the rank of sorted position e is e+1
           int a32 = 0;
 #pragma unroll
-          for (int r = 0; r < R; ++r) {
-            const uint32_t e = lane * R + r;
-            if (e < n_valid && !(key[r] & 1u)) a32 += 2 * (int)(e + 1);
-          }
-          acc = a32;
+          int npos = 0;
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (r < rem && !(key[r] & 1u)) { a32 += 2 * (r + 1); ++npos; }
+          acc = a32 + 2 * (int)(lane * R) * npos;
         } else {
 #pragma unroll
           for (int r = 0; r < R; ++r)
-            if (lane * R + r <= n_valid) sB[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+            if (r <= rem) sB[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
           if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
           __syncwarp();
           run_pass(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
@@ -405,7 +407,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         uint32_t *dst = seg == 1 ? sA : sB;
 #pragma unroll
         for (int r = 0; r < R; ++r)
-          if (lane * R + r <= n_valid) dst[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+          if (r <= rem) dst[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
         if (n_valid == 32u * R && lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
         if (any_tie) {
           long long tt = 0, unused = 0;
@@ -438,7 +440,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
         o->w_ties = w_ties;
       } else {
-        o->status |= (run_mw ? FM_S_MW_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u);
+        // fire-and-forget OR (the Wilcoxon launch, or the zero fill, wrote the word earlier in the stream)
+        if (run_mw || run_k) atomicOr(&o->status, (run_mw ? FM_S_MW_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u));
         o->mw_2u1 = pooled ? mw_2r1 - (long long)nb * ((long long)nb + 1) : 0;
         o->mw_2r1 = pooled ? mw_2r1 : 0;
         o->mw_ties = pooled ? mw_ties : 0;

@@ -49,20 +49,23 @@ FM_HD void fm_mw_walk(const uint32_t *A, int na, const uint32_t *B, int nb, cons
   int i = lo, j = p0 - lo;
   uint32_t ha = A[fm_pidx(i)], hb = B[fm_pidx(j)];
   uint32_t pa = i > 0 ? A[fm_pidx(i - 1)] : 0xFFFFFFFFu;  // previous baseline key (sentinel: none)
+  // Branch-free step (lanes disagree on which side to take at nearly every step, so an if/else
+  // body ran both sides each time): one select-addressed load through A with B at offset dB.
+  const int dB = (int)(B - A);
   for (int p = p0; p < p1; ++p) {
-    if (ha <= hb) {  // take a baseline sample; all current samples below it are already taken
-      plt += j;
-      if (ha == hb && ha != pa) {  // first of its run and it meets an equal current run (which starts at j)
-        const long long ca = rlA ? rlA[i] : 1, cb = rlB ? rlB[j] : 1;
-        peq += ca * cb;
-        x3 += ca * cb * (ca + cb);
-      }
-      pa = ha;
-      ++i;
-      ha = A[fm_pidx(i)];
-    } else {
-      ++j;
-      hb = B[fm_pidx(j)];
+    const bool take = ha <= hb;  // take a baseline sample; all current samples below it are already taken
+    if (take && ha == hb && ha != pa) {  // first of its run and it meets an equal current run (which starts at j)
+      const long long ca = rlA ? rlA[i] : 1, cb = rlB ? rlB[j] : 1;
+      peq += ca * cb;
+      x3 += ca * cb * (ca + cb);
     }
+    plt += take ? j : 0;
+    pa = take ? ha : pa;
+    i += take ? 1 : 0;
+    j += take ? 0 : 1;
+    const int idx = take ? i : j;
+    const uint32_t nxt = A[fm_pidx(idx) + (take ? 0 : dB)];
+    ha = take ? nxt : ha;
+    hb = take ? hb : nxt;
   }
 }
