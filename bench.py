@@ -376,7 +376,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--units", type=int, default=1_000_000, help="series-windows per GPU")
-    ap.add_argument("--cpu-units", type=int, default=131072, help="cpu_baseline sample (units)")
+    ap.add_argument("--cpu-units", type=int, default=1_000_000, help="cpu_baseline sample (units; ~5 s on 16 cores)")
     ap.add_argument("--ref-units", type=int, default=65536, help="--impl reference: units per step")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--hw-units", type=int, default=1_000_000, help="cfg4 Holt-Winters units (10080 points each)")

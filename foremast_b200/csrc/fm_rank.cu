@@ -374,6 +374,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
       // slots of this lane that hold real samples (compared against literals below: a bound written
       // as lane*R + r < n_valid gets hoisted into R loop-invariant registers, and those spilled)
       const int rem = (int)n_valid - (int)(lane * R);
+      // fm_pidx(lane*R + r) without a shift per key: the lane's slots start at pad0 and gain one pad
+      // word at each 32-element boundary they cross (slot `cross`, and cross + 32 when R > 32)
+      const int pad0 = fm_pidx((int)(lane * R)), cross = 32 - (int)((lane * R) & 31u);
       bool tie = false;
 #pragma unroll
       for (int r = 0; r + 1 < R; ++r) tie = tie || (((key[r] >> sh) == (key[r + 1] >> sh)) && (r + 1 < rem));
@@ -395,7 +398,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         } else {
 #pragma unroll
           for (int r = 0; r < R; ++r)
-            if (r <= rem) sB[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+            if (r <= rem) sB[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
           if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
           __syncwarp();
           run_pass(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
@@ -407,7 +410,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         uint32_t *dst = seg == 1 ? sA : sB;
 #pragma unroll
         for (int r = 0; r < R; ++r)
-          if (r <= rem) dst[fm_pidx(lane * R + r)] = key[r];  // element n_valid is a sentinel already
+          if (r <= rem) dst[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
         if (n_valid == 32u * R && lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
         if (any_tie) {
           long long tt = 0, unused = 0;
@@ -422,7 +425,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
       __syncwarp();
       int plt;
       long long peq, x3;
-      fm_mw_walk(sA, (int)nb, sB, (int)nc, tie_a ? rlA : nullptr, tie_b ? rlB : nullptr, (int)lane, plt, peq, x3);
+      fm_mw_walk(sA, (kTile / 33) * 32, (int)nb, (int)nc, tie_a ? rlA : nullptr, tie_b ? rlB : nullptr, (int)lane, plt, peq, x3);
       const long long plt_sum = warp_sum_i64((long long)plt), peq_sum = warp_sum_i64(peq);
       mw_2r1 = (long long)nb * ((long long)nb + 1) + 2 * plt_sum + peq_sum;
       mw_ties = warp_sum_i64(mw_ties + 3 * x3);
@@ -487,7 +490,10 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
   const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
-  const int tile_words = seg_cap + (seg_cap >> 5) + 2, rl_entries = (seg_cap + 2 + 1) & ~1;
+  // the two sorted runs of a unit share one element space: the second starts at element K, a multiple
+  // of 32 that leaves room for the first run and its sentinel (fm_rank_merge.h)
+  const int K = (seg_cap + 1 + 31) / 32 * 32;
+  const int tile_words = K + K / 32, rl_entries = (seg_cap + 2 + 1) & ~1;
   const int smem = kWarpsPerBlock * 2 * (tile_words * 4 + rl_entries * 2);
   const int raw_cap = (seg_cap + 3) & ~3;
   const int smem_w = kWarpsPerBlock * ((33 * R + 2) * 4 + 2 * raw_cap * 4);

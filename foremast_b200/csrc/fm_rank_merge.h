@@ -26,11 +26,13 @@
 // stores (lane stride R words) and the walk's reads spread over banks
 FM_HD int fm_pidx(int e) { return e + (e >> 5); }
 
-// A, B: sorted order-preserving u32 keys, each followed by a 0xFFFFFFFF sentinel at index na / nb.
+// T: one tile holding both sorted runs of order-preserving u32 keys in a single element space --
+// baseline element e at T[fm_pidx(e)], current element e at T[fm_pidx(K + e)], K a multiple of 32
+// (so fm_pidx(K + e) = fm_pidx(K) + fm_pidx(e)) -- each run followed by a 0xFFFFFFFF sentinel.
 // rlA / rlB: run length stored at the index of each run's first element (read only there), or
 // nullptr when that sample has no equal values at all (every run has length 1).
-FM_HD void fm_mw_walk(const uint32_t *A, int na, const uint32_t *B, int nb, const uint16_t *rlA, const uint16_t *rlB,
-                      int lane, int &plt, long long &peq, long long &x3) {
+FM_HD void fm_mw_walk(const uint32_t *T, int K, int na, int nb, const uint16_t *rlA, const uint16_t *rlB, int lane,
+                      int &plt, long long &peq, long long &x3) {
   const int n = na + nb, c = (n + 31) >> 5;
   int p0 = lane * c;
   if (p0 > n) p0 = n;
@@ -44,28 +46,29 @@ FM_HD void fm_mw_walk(const uint32_t *A, int na, const uint32_t *B, int nb, cons
   int lo = p0 > nb ? p0 - nb : 0, hi = p0 < na ? p0 : na;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
-    if (A[fm_pidx(mid)] <= B[fm_pidx(p0 - 1 - mid)]) lo = mid + 1; else hi = mid;
+    if (T[fm_pidx(mid)] <= T[fm_pidx(K + p0 - 1 - mid)]) lo = mid + 1; else hi = mid;
   }
-  int i = lo, j = p0 - lo;
-  uint32_t ha = A[fm_pidx(i)], hb = B[fm_pidx(j)];
-  uint32_t pa = i > 0 ? A[fm_pidx(i - 1)] : 0xFFFFFFFFu;  // previous baseline key (sentinel: none)
+  const int i0 = lo;
+  int i = lo, jk = K + p0 - lo;  // heads: baseline element i, current element jk - K
+  uint32_t ha = T[fm_pidx(i)], hb = T[fm_pidx(jk)];
+  uint32_t pa = i > 0 ? T[fm_pidx(i - 1)] : 0xFFFFFFFFu;  // previous baseline key (sentinel: none)
   // Branch-free step (lanes disagree on which side to take at nearly every step, so an if/else
-  // body ran both sides each time): one select-addressed load through A with B at offset dB.
-  const int dB = (int)(B - A);
+  // body ran both sides each time): one load at a selected element index of the shared space.
+  int acc = 0;  // sum of jk over the baseline samples taken; K * (their count) comes off at the end
   for (int p = p0; p < p1; ++p) {
     const bool take = ha <= hb;  // take a baseline sample; all current samples below it are already taken
-    if (take && ha == hb && ha != pa) {  // first of its run and it meets an equal current run (which starts at j)
-      const long long ca = rlA ? rlA[i] : 1, cb = rlB ? rlB[j] : 1;
+    if (take && ha == hb && ha != pa) {  // first of its run and it meets an equal current run (which starts at jk)
+      const long long ca = rlA ? rlA[i] : 1, cb = rlB ? rlB[jk - K] : 1;
       peq += ca * cb;
       x3 += ca * cb * (ca + cb);
     }
-    plt += take ? j : 0;
+    acc += take ? jk : 0;
     pa = take ? ha : pa;
     i += take ? 1 : 0;
-    j += take ? 0 : 1;
-    const int idx = take ? i : j;
-    const uint32_t nxt = A[fm_pidx(idx) + (take ? 0 : dB)];
+    jk += take ? 0 : 1;
+    const uint32_t nxt = T[fm_pidx(take ? i : jk)];
     ha = take ? nxt : ha;
     hb = take ? hb : nxt;
   }
+  plt = acc - K * (i - i0);
 }
