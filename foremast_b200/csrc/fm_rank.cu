@@ -98,10 +98,12 @@ __device__ __forceinline__ void lane_bitonic_merge(uint32_t (&v)[R]) {
   }
   if constexpr (odd_part(R) == 3) {
 #pragma unroll
-    for (int g = 0; g < R; g += 3) {
-      cex(v[g], v[g + 1]);
-      cex(v[g + 1], v[g + 2]);
-      cex(v[g], v[g + 1]);
+    for (int g = 0; g < R; g += 3) {  // 3-sorter in four ALU ops: min3, max3, and the middle by subtraction (mod 2^32)
+      const uint32_t lo = __vimin3_u32(v[g], v[g + 1], v[g + 2]), hi = __vimax3_u32(v[g], v[g + 1], v[g + 2]);
+      const uint32_t mid = v[g] + v[g + 1] + v[g + 2] - lo - hi;
+      v[g] = lo;
+      v[g + 1] = mid;
+      v[g + 2] = hi;
     }
   }
 }
@@ -344,9 +346,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
           const uint32_t e = r * 32 + lane;
           uint32_t k = kKeySentinel;
           if (e < m) {
-            const float d = rawB[e] - rawA[e];
-            if (d != 0.0f) {
-              k = (__float_as_uint(fabsf(d)) << 1) | (d < 0.0f ? 1u : 0u);
+            // |d| bits << 1 with the sign in bit 0 is a rotate; +-0 rotate to 0 / 1
+            const uint32_t du = __float_as_uint(rawB[e] - rawA[e]), rot = __funnelshift_l(du, du, 1);
+            if (rot > 1u) {
+              k = rot;
               ++nz;
             }
           }
