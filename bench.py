@@ -262,8 +262,16 @@ def run_ours(args):
     pv = pinned.view(np.float32)
     pv[:] = host.values
     host_p = abi.HostCsr.__new__(abi.HostCsr)
-    host_p.values, host_p.offsets, host_p.seg_lens = pv, host.offsets, host.seg_lens
-    host_p.service_id, host_p.metric_type = host.service_id, host.metric_type
+    pins = [(pinned, pin_ptr)]
+
+    def pin(a):  # the per-unit arrays live in pinned memory too, like the samples
+        buf, ptr = ctx.host_alloc(a.nbytes)
+        pins.append((buf, ptr))
+        out = buf.view(a.dtype).reshape(a.shape)
+        out[...] = a
+        return out
+    host_p.values, host_p.offsets, host_p.seg_lens = pv, pin(host.offsets), pin(host.seg_lens)
+    host_p.service_id, host_p.metric_type = pin(host.service_id), pin(host.metric_type)
     h2d = pv.nbytes + host.offsets.nbytes + host.seg_lens.nbytes + host.service_id.nbytes + host.metric_type.nbytes
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     ctx.score_host(host_p, p, total_services)  # warm-up
@@ -343,7 +351,9 @@ def run_ours(args):
                                 "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
         }
         OUT.emit(json.dumps(line))
-    ctx.host_free(pin_ptr)
+    del host_p
+    for _, ptr in pins:
+        ctx.host_free(ptr)
     batch.free()
     ctx.close()
     if world > 1:
