@@ -334,7 +334,10 @@ def run_ours(args):
                                                "band": "k_band", "verdict": "k_verdict_reduce"}[dom],
                          "achieved": kernels[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                          "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
-                         "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0},
+                         "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0,
+                         "note": ("the rank kernels are bound by the ALU pipe (integer min/max of the sorting network, "
+                                  "81-83 % busy in profiles/r1_final2_rank_band.md), not by HBM; the HBM-bound kernels of "
+                                  "this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None},
             "kernels": kernels,
             "other_configs": other,
             "cpu_baseline": ({"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
