@@ -265,7 +265,9 @@ void fm_batch_free(fm_batch *b);
 
 /* The scoring pass itself: pairwise tests -> threshold adjust -> band models -> anomaly flags ->
  * per-service verdicts (docs/guides/design.md:35,43).  Asynchronous on the context's stream;
- * accessors synchronise. */
+ * accessors synchronise.  Limits: with a pairwise test enabled, baseline and current segments may
+ * hold at most 2048 samples each (FM_E_UNSUPPORTED beyond; the reference's windows are 30-1440
+ * one-minute points); history length is only bounded by memory. */
 int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out);
 /* One-shot, host in / host out: chunked H2D overlapped with scoring, verdicts copied back.
  * `verdicts` has room for n_services entries. */
