@@ -90,6 +90,12 @@ cudaError_t fm_launch_hw_fit(const DevBatch &b, const DevParams *dp, uint32_t pe
 cudaError_t fm_launch_hw_resume(const DevBatch &b, const DevParams *dp, uint32_t period, double *state,
                                 fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points, int sm_count,
                                 cudaStream_t st);
+// fm_hw_tm.cu: the same five modes with the seasonals in tensor memory (period % 32 == 0)
+bool fm_hw_tm_supported(uint32_t period);
+cudaError_t fm_launch_hw_tm(int mode, const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                            uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                            const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state,
+                            int sm_count, cudaStream_t st);
 uint64_t fm_scan_scratch_bytes(uint64_t n);
 cudaError_t fm_launch_scan_counts(const void *in, size_t stride, uint64_t n, unsigned long long *out,
                                   unsigned long long *scratch, cudaStream_t st);

@@ -1,0 +1,519 @@
+// fm_hw_tm.cu -- Holt-Winters scoring with the seasonal state in TENSOR MEMORY.
+//
+// Same model, same reduce-then-scan formulation and the same modes as fm_hw.cu (see there for the
+// reference citations and the maths); what changes is where the period-long seasonal array lives.
+// k_hw keeps it in shared memory, 8 B x period per unit (11.25 KB at period 1440), and that is what
+// caps it at 12 warps per SM -- the kernel is latency-bound, so occupancy is its speed.  Here a
+// super-tile is exactly one season (32*k samples, k = period/32), so lane `l` meets the SAME k
+// seasonal slots in every super-tile: the array is lane-private, and Blackwell's tensor memory
+// (256 KB per SM: 128 lanes x 512 32-bit columns, each thread of a warp reaching the columns of its
+// own lane with tcgen05.ld/st.32x32b) holds it as plain scratch -- no tensor-core instruction is
+// involved.  Shared memory then carries only the fp32 samples of the season (5.6 KB per unit) and
+// one CTA of 20 warps per SM runs 20 units at a time instead of 12.  Seasonals move between tensor
+// memory and registers eight at a time (16 columns), so the inner loops also lose their per-sample
+// LDS/STS and all of k_hw's wrap-around index handling (storage is indexed by the position inside
+// the lane's chunk, never by the absolute slot).
+// Used when period % 32 == 0; other periods take k_hw.
+#include <algorithm>
+
+#include "fm_common.cuh"
+
+namespace {
+
+constexpr int kMaxWarps = 16;
+
+struct V2 { double l, b; };
+
+__device__ __forceinline__ V2 matvec(const double *m, V2 v) {  // m = {a00, a01, a10, a11}
+  V2 r;
+  r.l = fma(m[0], v.l, m[1] * v.b);
+  r.b = fma(m[2], v.l, m[3] * v.b);
+  return r;
+}
+
+// eight seasonals = 16 columns of this thread's tensor-memory lane
+__device__ __forceinline__ void tm_ld8(uint32_t taddr, double (&d)[8]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+  for (int j = 0; j < 8; ++j) d[j] = __hiloint2double((int)r[2 * j + 1], (int)r[2 * j]);
+}
+
+__device__ __forceinline__ void tm_st8(uint32_t taddr, const double (&d)[8]) {
+  uint32_t r[16];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    r[2 * j] = (uint32_t)__double2loint(d[j]);
+    r[2 * j + 1] = (uint32_t)__double2hiint(d[j]);
+  }
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};\n" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+
+// MODE as in fm_hw.cu: 0 score, 1 score + bands, 2 emit pass of the anomaly list, 3 fit (model
+// window only, state saved), 4 resume (score the current segment from the saved state, advance it).
+template <int MODE>
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const DevParams *__restrict__ dp,
+                                                             fm_series_score *__restrict__ scores,
+                                                             uint32_t *__restrict__ unit_status,
+                                                             uint32_t *__restrict__ unit_points,
+                                                             float *__restrict__ band_up, float *__restrict__ band_lo,
+                                                             const unsigned long long *__restrict__ emit_off,
+                                                             uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val,
+                                                             double *__restrict__ state) {
+  constexpr bool BANDS = MODE == 1, EMIT = MODE == 2, FIT = MODE == 3, RESUME = MODE == 4;
+  extern __shared__ float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
+  __shared__ uint32_t s_tm_base;
+  __shared__ double s_apow[5 * 4];
+  const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+  const uint32_t m = dp->period, k = m / 32, kb = (k + 7) / 8;  // kb blocks of eight seasonals per lane
+  float *const Xb = s_x + (size_t)warp * 2 * m;
+
+  // ---- tensor memory: the CTA takes all 512 columns; warp w works in lane quarter w % 4 (the only
+  //      lanes its tcgen05.ld/st can reach) and column range (w / 4) * 16 * kb
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(&s_tm_base)),
+                 "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_pow[threadIdx.x];
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n");
+  const uint32_t tm_base = s_tm_base;
+  const uint32_t tS = tm_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * 16u * kb;
+
+  const double alpha = dp->alpha, ab = dp->alpha * dp->beta, g1 = dp->gamma * (1.0 - dp->alpha);
+  // A^2 and A*g for the two-samples-per-step form of the recurrence (fm_hw.cu)
+  const double a1 = 1.0 - alpha, d1 = 1.0 - ab;
+  const double a2[4] = {a1 * a1 - a1 * ab, a1 * a1 + a1 * d1, -ab * a1 - ab * d1, -ab * a1 + d1 * d1};
+  const double agl = a1 * alpha + a1 * ab, agb = -ab * alpha + d1 * ab;
+  const double *const Apow = s_apow;  // A^(k*2^i), i = 0..4
+  const double Alane[4] = {dp->hw_lane[4 * lane], dp->hw_lane[4 * lane + 1], dp->hw_lane[4 * lane + 2],
+                           dp->hw_lane[4 * lane + 3]};  // A^(k*lane)
+  const uint32_t p0 = lane * k;  // this lane's chunk inside a season-long super-tile
+
+  for (uint64_t u = (uint64_t)blockIdx.x * n_warps + warp; u < b.n_units; u += (uint64_t)gridDim.x * n_warps) {
+    const int64_t off = b.offsets[u];
+    const uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
+    uint32_t a0 = 0, ns = 0;
+    if (nh >= dp->min_historical && nh > 0) { a0 = 0; ns = nh; }
+    else if (nb >= dp->min_historical && nb > 0) { a0 = nh; ns = nb; }
+    double *const ust = (FIT || RESUME) ? state + u * (uint64_t)(m + 4) : nullptr;  // {l, b, sigma, phase | -1, S[m]}
+    if (FIT) {
+      if ((uint64_t)ns < 2ull * m) {
+        if (lane == 0) ust[3] = -1.0;  // no model for this unit
+        continue;
+      }
+    } else if (RESUME) {
+      const bool ok = nc > 0 && ust[3] >= 0.0;
+      if (!ok) {
+        if (lane == 0) {
+          fm_series_score *o = scores + u;
+#pragma unroll
+          for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
+          o->status = FM_S_UNKNOWN;
+          o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
+          unit_status[u] = FM_S_UNKNOWN;
+          unit_points[u] = 0;
+        }
+        continue;
+      }
+      ns = 0;
+    } else if (ns == 0 || nc == 0 || (uint64_t)ns < 2ull * m) {
+      continue;  // unknown unit, or not two seasons of model window
+    }
+    unsigned long long emit_base = 0;
+    if (EMIT) {
+      emit_base = emit_off[u];
+      if (emit_off[u + 1] == emit_base) continue;
+    }
+    const uint32_t c0 = nh + nb, n_stream = FIT ? ns : ns + nc;
+    const float *unit = b.values + off;
+
+    uint32_t st = (FIT || RESUME) ? 0u : scores[u].status;
+    const DevRule &dr = dp->rules[b.metric_type[u] < FM_MAX_METRIC_TYPES ? b.metric_type[u] : 0];
+    const double kk = (st & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
+    const double mlb = dr.min_lower_bound;
+    const uint32_t bound = dr.bound;
+
+    // 4-byte async copies of stream positions [q0s, q0s + m) into one of the two sample buffers, all
+    // in flight together (segments are only 4 B aligned in general); completion is awaited later
+    auto stage = [&](uint32_t q0s, float *dst) {
+      const uint32_t nv = min(m, n_stream - q0s);
+      if (q0s + nv <= ns || q0s >= ns) {  // one segment: one contiguous source
+        const float *src = unit + (q0s < ns ? a0 + q0s : c0 + (q0s - ns));
+#pragma unroll 9
+        for (uint32_t i = lane; i < nv; i += 32) cp_async4(dst + i, src + i);
+      } else {
+        for (uint32_t i = lane; i < nv; i += 32) {
+          const uint32_t q = q0s + i;
+          cp_async4(dst + i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+        }
+      }
+      cp_async_commit();
+    };
+
+    V2 carry;
+    double sse = 0.0, sigma = 0.0;
+    bool sigma_ready = false;
+    uint32_t phase = 0;  // seasonal slot of stream position 0
+    uint32_t cur = 0;  // buffer that holds (or is receiving) the super-tile at q0
+    __syncwarp();      // the previous unit is done with both buffers
+    if (RESUME) {
+      stage(0, Xb);
+      carry.l = ust[0];
+      carry.b = ust[1];
+      sigma = ust[2];
+      sigma_ready = true;
+      phase = (uint32_t)ust[3];
+      for (uint32_t blk = 0; blk < kb; ++blk) {
+        double s[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t i = 8 * blk + j;
+          s[j] = i < k ? ust[4 + (phase + p0 + i) % m] : 0.0;
+        }
+        tm_st8(tS + 16 * blk, s);
+      }
+    } else {
+      // ---- initialisation from the first two seasons (D5); both lie inside the model window.  The
+      //      second one is also the first super-tile scored below, so it stays where it lands.
+      stage(0, Xb);
+      stage(m, Xb + m);
+      cp_async_wait<1>();
+      __syncwarp();
+      double s0 = 0.0, s1 = 0.0;
+      for (uint32_t i = lane; i < m; i += 32) s0 += (double)Xb[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+      const double L0 = s0 / (double)m;
+      for (uint32_t blk = 0; blk < kb; ++blk) {
+        double s[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t i = 8 * blk + j;
+          s[j] = i < k ? (double)Xb[p0 + i] - L0 : 0.0;
+        }
+        tm_st8(tS + 16 * blk, s);
+      }
+      cp_async_wait<0>();
+      __syncwarp();
+      for (uint32_t i = lane; i < m; i += 32) s1 += (double)Xb[m + i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      const double M2 = s1 / (double)m;
+      carry.l = L0;
+      carry.b = (M2 - L0) / (double)m;
+      cur = 1;
+    }
+    tm_wait_st();
+    uint32_t n_anom = 0, first = FM_NONE_IDX;
+
+    for (uint32_t q0 = RESUME ? 0u : m; q0 < n_stream; q0 += m, cur ^= 1u) {
+      // this super-tile has landed and every lane is done with the other buffer: start the next one
+      cp_async_wait<0>();
+      __syncwarp();
+      if (q0 + m < n_stream) stage(q0 + m, Xb + (cur ^ 1u) * m);
+      const uint32_t qa = q0 + p0;                                      // stream position of the chunk
+      const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
+      const float *const xp = Xb + cur * m + p0;
+
+      // ---- pass 1: chunk offset from a zero state (chunks past the end of the stream only feed
+      //      lanes that are past the end too).  Two samples per step: v'' = A^2 v + (A g y1 + g y2).
+      V2 uo;
+      uo.l = 0.0;
+      uo.b = 0.0;
+      auto pair_off = [&](uint32_t i, double sa, double sb) {
+        const double y1 = (double)xp[i] - sa, y2 = (double)xp[i + 1] - sb;
+        const double cl = fma(agl, y1, alpha * y2), cb = fma(agb, y1, ab * y2);
+        const double nl = fma(a2[0], uo.l, fma(a2[1], uo.b, cl));
+        const double nb2 = fma(a2[2], uo.l, fma(a2[3], uo.b, cb));
+        uo.l = nl;
+        uo.b = nb2;
+      };
+      for (uint32_t blk = 0; blk < kb; ++blk) {
+        double s[8];
+        tm_ld8(tS + 16 * blk, s);
+        // blocks that are whole in every lane (all but the last one or two of a super-tile) run
+        // straight-line; the guarded form is for the ragged end of a chunk or of the stream
+        if (__all_sync(0xffffffffu, 8 * blk + 8 <= kv)) {
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) pair_off(8 * blk + j, s[j], s[j + 1]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) {
+            const uint32_t i = 8 * blk + j;
+            if (i + 1 < kv) {
+              pair_off(i, s[j], s[j + 1]);
+            } else if (i < kv) {
+              const double y = (double)xp[i] - s[j];
+              const double t = uo.l + uo.b, w = y - t;
+              uo.l = fma(alpha, w, t);
+              uo.b = fma(ab, w, uo.b);
+            }
+          }
+        }
+      }
+      // ---- inclusive scan of the chunk maps v -> A^k v + u
+      V2 inc = uo;
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int o = 1 << i;
+        V2 p;
+        p.l = __shfl_up_sync(0xffffffffu, inc.l, o);
+        p.b = __shfl_up_sync(0xffffffffu, inc.b, o);
+        if ((int)lane >= o) {
+          const V2 t = matvec(Apow + 4 * i, p);
+          inc.l += t.l;
+          inc.b += t.b;
+        }
+      }
+      V2 vin;  // state entering this lane's chunk
+      vin.l = __shfl_up_sync(0xffffffffu, inc.l, 1);
+      vin.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
+      if (lane == 0) { vin.l = 0.0; vin.b = 0.0; }
+      {
+        const V2 cv = matvec(Alane, carry);
+        vin.l += cv.l;
+        vin.b += cv.b;
+      }
+
+      // ---- pass 2: the real recurrence over the chunk; flags collected in a 64-bit mask (k <= 64).
+      //      Sweep 0 takes the samples of the model window, sweep 1 the current ones (sigma must be
+      //      final first); each sweep walks the seasonals block by block through registers.
+      double l = vin.l, bb = vin.b;
+      unsigned long long fmask = 0ull;
+      const bool tile_has_cur = q0 + m > ns;
+      const uint32_t i_m = qa < ns ? min(kv, ns - qa) : 0u;  // model samples at the head of the chunk
+      for (int sweep = 0; sweep < 2; ++sweep) {
+        if (sweep == 0 && q0 >= ns) continue;   // nothing of the model window in this super-tile
+        if (sweep == 1) {
+          if (!tile_has_cur) break;
+          if (!sigma_ready) {  // the model window ends in this super-tile: close the residual sum first
+            double t = sse;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            sigma = sqrt(t / (double)(ns - m));
+            sigma_ready = true;
+          }
+        }
+        const uint32_t lo = sweep ? i_m : 0u, hi = sweep ? kv : i_m;
+        // one sample: one-step error, state and season update, residual sum or flag
+        auto single_step = [&](uint32_t i, double &seas) {
+          const double x = (double)xp[i];
+          const double lb = l + bb, f = lb + seas, e = x - f;
+          l = fma(alpha, e, lb);
+          bb = fma(ab, e, bb);
+          if (sweep == 0) {
+            sse = fma(e, e, sse);
+          } else {
+            const double up = fma(kk, sigma, f);
+            double lw = fma(-kk, sigma, f);
+            lw = lw < mlb ? mlb : lw;
+            // guarded comparison (DECISIONS "HW"): excursions below 1e-9 relative do not count
+            const double gx = 1e-9 * (fabs(f) + fabs(x));
+            if (((bound & 1u) && x - up > gx) || ((bound & 2u) && lw - x > gx)) fmask |= 1ull << i;
+            if (BANDS) {
+              band_up[off + c0 + (qa + i - ns)] = (float)up;
+              band_lo[off + c0 + (qa + i - ns)] = (float)lw;
+            }
+          }
+          seas = fma(g1, e, seas);
+        };
+        // two samples: the state two samples ahead comes straight from A^2 (short dependent chain);
+        // the state one sample ahead, the two one-step errors and the season updates hang off it
+        auto pair_step = [&](uint32_t i, double &sq1, double &sq2) {
+          const double x1 = (double)xp[i], x2 = (double)xp[i + 1], s1 = sq1, s2 = sq2;
+          const double y1 = x1 - s1, y2 = x2 - s2;
+          const double lb1 = l + bb, e1 = y1 - lb1;
+          const double l1 = fma(alpha, e1, lb1), b1 = fma(ab, e1, bb);
+          const double cl = fma(agl, y1, alpha * y2), cb = fma(agb, y1, ab * y2);
+          const double l2 = fma(a2[0], l, fma(a2[1], bb, cl)), b2 = fma(a2[2], l, fma(a2[3], bb, cb));
+          const double lb2 = l1 + b1, e2 = y2 - lb2;
+          sq1 = fma(g1, e1, s1);
+          sq2 = fma(g1, e2, s2);
+          if (sweep == 0) {
+            sse = fma(e1, e1, sse);
+            sse = fma(e2, e2, sse);
+          } else {
+            const double f1 = lb1 + s1, f2 = lb2 + s2;
+            const double up1 = fma(kk, sigma, f1), up2 = fma(kk, sigma, f2);
+            double lo1 = fma(-kk, sigma, f1), lo2 = fma(-kk, sigma, f2);
+            lo1 = lo1 < mlb ? mlb : lo1;
+            lo2 = lo2 < mlb ? mlb : lo2;
+            const double g1x = 1e-9 * (fabs(f1) + fabs(x1)), g2x = 1e-9 * (fabs(f2) + fabs(x2));
+            if (((bound & 1u) && x1 - up1 > g1x) || ((bound & 2u) && lo1 - x1 > g1x)) fmask |= 1ull << i;
+            if (((bound & 1u) && x2 - up2 > g2x) || ((bound & 2u) && lo2 - x2 > g2x)) fmask |= 2ull << i;
+            if (BANDS) {
+              const int64_t at = off + c0 + (qa + i - ns);
+              band_up[at] = (float)up1; band_lo[at] = (float)lo1;
+              band_up[at + 1] = (float)up2; band_lo[at + 1] = (float)lo2;
+            }
+          }
+          l = l2;
+          bb = b2;
+        };
+        for (uint32_t blk = 0; blk < kb; ++blk) {
+          double s[8];
+          tm_ld8(tS + 16 * blk, s);
+          if (__all_sync(0xffffffffu, lo <= 8 * blk && 8 * blk + 8 <= hi)) {  // whole block, every lane
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) pair_step(8 * blk + j, s[j], s[j + 1]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              const uint32_t i = 8 * blk + j;
+              if (i >= lo && i + 1 < hi) {
+                pair_step(i, s[j], s[j + 1]);
+              } else {
+                if (i >= lo && i < hi) single_step(i, s[j]);
+                if (i + 1 >= lo && i + 1 < hi) single_step(i + 1, s[j + 1]);
+              }
+            }
+          }
+          tm_st8(tS + 16 * blk, s);
+        }
+        tm_wait_st();
+      }
+      // next super-tile's carry (and the state the model cache keeps): the state after the last real
+      // sample of this super-tile, which lives in lane (nv-1)/k
+      {
+        const uint32_t nv = min(m, n_stream - q0);
+        const int src = (int)((nv - 1) / k);
+        carry.l = __shfl_sync(0xffffffffu, l, src);
+        carry.b = __shfl_sync(0xffffffffu, bb, src);
+      }
+      if (tile_has_cur) {
+        const uint32_t cnt = __popcll(fmask);
+        uint32_t pre = cnt;  // exclusive prefix of flag counts over lanes (chunks are in stream order)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, pre, o);
+          if ((int)lane >= o) pre += t;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+        pre -= cnt;
+        if (total) {
+          const unsigned has = __ballot_sync(0xffffffffu, cnt != 0);
+          if (n_anom == 0) {
+            const int src = __ffs(has) - 1;
+            const uint32_t cand = qa + (uint32_t)(__ffsll((long long)fmask) - 1) - ns;
+            first = __shfl_sync(0xffffffffu, cand, src);
+          }
+          if (EMIT) {
+            unsigned long long mk = fmask;
+            uint32_t r = 0;
+            while (mk) {
+              const int bit = __ffsll((long long)mk) - 1;
+              mk &= mk - 1;
+              const unsigned long long at = emit_base + n_anom + pre + r++;
+              emit_idx[at] = qa + bit - ns;
+              emit_val[at] = xp[bit];
+            }
+          }
+          n_anom += total;
+        }
+      }
+    }
+    if (FIT || RESUME) {  // save the model: state after the last sample, residual sigma, phase, seasonals
+      if (FIT && !sigma_ready) {
+        double t = sse;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        sigma = sqrt(t / (double)(ns - m));
+      }
+      for (uint32_t blk = 0; blk < kb; ++blk) {
+        double s[8];
+        tm_ld8(tS + 16 * blk, s);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t i = 8 * blk + j;
+          if (i < k) ust[4 + (phase + p0 + i) % m] = s[j];
+        }
+      }
+      if (lane == 0) {
+        ust[0] = carry.l;
+        ust[1] = carry.b;
+        ust[2] = sigma;
+        ust[3] = (double)((phase + n_stream) % m);
+      }
+      __syncwarp();
+    }
+    if (lane == 0 && !EMIT && !FIT) {
+      fm_series_score *o = scores + u;
+      if (RESUME) {
+#pragma unroll
+        for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
+        o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
+        o->k_eff = kk;
+        unit_points[u] = 0;
+      }
+      st |= 1u << (FM_S_ALG_SHIFT + 4);
+      if (n_anom > 0 && n_anom >= dp->min_anomaly_points) st |= FM_S_ANOMALY;
+      o->status = st;
+      o->n_anom[4] = n_anom;
+      o->first_idx[4] = first;
+      o->sigma[4] = sigma;
+      unit_status[u] = st;
+      unit_points[u] = max(unit_points[u], n_anom);
+    }
+  }
+
+  // ---- give the tensor memory back
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tm_base), "n"(512));
+}
+
+template <int MODE>
+cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                      uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                      const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state, int sm_count,
+                      cudaStream_t st) {
+  const uint32_t k = period / 32, kb = (k + 7) / 8;
+  // warps per CTA: four lane quarters x as many 16*kb-column ranges as fit in 512 columns, capped by
+  // the launch bound and by the fp32 season each warp keeps in shared memory
+  int warps = (int)std::min<uint32_t>(4 * (512 / (16 * kb)), kMaxWarps);
+  warps = std::min(warps, (220 * 1024) / ((int)period * 8));
+  if (warps < 1) return cudaErrorInvalidValue;
+  uint64_t blocks = (b.n_units + warps - 1) / warps;
+  const uint64_t cap = (uint64_t)sm_count;  // persistent: one CTA is resident per SM (it owns the tensor memory)
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) return cudaSuccess;
+  const int smem = warps * 2 * (int)period * (int)sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(k_hw_tm<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  k_hw_tm<MODE><<<(unsigned)blocks, warps * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
+                                                           emit_off, emit_idx, emit_val, state);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+bool fm_hw_tm_supported(uint32_t period) { return period >= 32 && period % 32 == 0 && period <= 2048; }
+
+cudaError_t fm_launch_hw_tm(int mode, const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                            uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                            const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state,
+                            int sm_count, cudaStream_t st) {
+  switch (mode) {
+    case 0: return launch_tm<0>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx, emit_val, state, sm_count, st);
+    case 1: return launch_tm<1>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx, emit_val, state, sm_count, st);
+    case 2: return launch_tm<2>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx, emit_val, state, sm_count, st);
+    case 3: return launch_tm<3>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx, emit_val, state, sm_count, st);
+    case 4: return launch_tm<4>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx, emit_val, state, sm_count, st);
+  }
+  return cudaErrorInvalidValue;
+}
