@@ -187,10 +187,16 @@ def test_rolling_window_sizes(ctx, oracle, window):
 
 @pytest.mark.parametrize("shape,period,n", [((400, 0, 90), 96, 600), ((10080, 0, 60), 1440, 150),
                                             ((2900, 30, 1500), 1440, 100), ((64, 0, 33), 32, 300),
-                                            ((5000, 40, 40), 2048, 64)])
-def test_holt_winters(ctx, oracle, shape, period, n):
+                                            ((5000, 40, 40), 2048, 64), ((700, 0, 150), 100, 300),
+                                            ((3000, 0, 700), 1000, 80)])
+@pytest.mark.parametrize("seasonals", ["tensor_memory", "shared_memory"])
+def test_holt_winters(ctx, oracle, shape, period, n, seasonals, monkeypatch):
     """BASELINE.json configs[3]: Holt-Winters seasonal (period 1440, 7-day history), continuous mode.
-    The kernel scans each 32-sample tile in parallel, so floats are compared at 1e-5 relative."""
+    The kernels scan each season in parallel, so floats are compared at 1e-5 relative.  Periods that
+    are multiples of 32 keep the seasonals in tensor memory (k_hw_tm), the others (100, 1000 here) in
+    shared memory (k_hw); FOREMAST_GPU_HW_SMEM forces the latter so both run on every shape."""
+    if seasonals == "shared_memory":
+        monkeypatch.setenv("FOREMAST_GPU_HW_SMEM", "1")
     b = ctx.batch_synth(n, *shape, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=period)
     p = full_params(oracle, abi.ALG_HW | abi.ALG_MA_ALL, abi.PW_ALL)
     p.period = period
@@ -213,7 +219,7 @@ def test_holt_winters(ctx, oracle, shape, period, n):
     b.free()
 
 
-@pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400)])
+@pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400), (100, 777)])
 def test_model_cache_continuous_mode(ctx, oracle, period, hist):
     """Continuous mode: fit Holt-Winters once, then score successive current windows from the cached
     state.  Must equal one oracle pass over history + all windows (sigma is the fit's)."""
