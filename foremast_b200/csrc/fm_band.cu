@@ -14,6 +14,8 @@
 // memory ring, and each lane then walks its own row with conflict-free 128-bit LDS (row stride
 // 36 words).  Algorithmic bytes per unit: 4*(n_hist+n_base+n_cur) + 8 (offset) + 12 (lengths)
 // + results.
+#include <algorithm>
+
 #include "fm_common.cuh"
 
 namespace {
@@ -21,12 +23,12 @@ namespace {
 constexpr int kChunk = 32;        // samples per row per stage
 constexpr int kRowWords = 36;     // 32 + 4 pad words: 16 B aligned rows, conflict-free LDS.128
 constexpr int kStages = 2;        // current chunk + one in flight (deeper rings cost occupancy: 3 -> 2 gained 12 %)
-constexpr int kWarpsPerBlock = 8;
+constexpr int kWarpsPerBlock = 8;  // launch bound; small batches run 6-warp blocks (launch_mode)
 // Variants with the rolling band keep one more slot: the chunk BEFORE the current one stays intact,
 // so the lagging sample (W <= 32 back) comes from shared memory instead of a scattered global load.
 __host__ __device__ constexpr int ring_slots(uint32_t algs) { return (algs & FM_ALG_MA_ROLLING) ? kStages + 1 : kStages; }
-__host__ __device__ constexpr int ring_bytes(uint32_t algs) { return kWarpsPerBlock * ring_slots(algs) * 32 * kRowWords * 4; }
-constexpr int kLoBytes = kWarpsPerBlock * 32 * kRowWords * 4;  // MODE 1: staging of the lower band, one chunk per warp
+__host__ __device__ constexpr int ring_bytes(uint32_t algs, int wpb) { return wpb * ring_slots(algs) * 32 * kRowWords * 4; }
+__host__ __device__ constexpr int lo_bytes(int wpb) { return wpb * 32 * kRowWords * 4; }  // MODE 1: staging of the lower band, one chunk per warp
 
 struct Rule {
   double k, mlb;
@@ -234,12 +236,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   constexpr int kSlots = ring_slots(ALGS);
-  constexpr int kRingB = ring_bytes(ALGS);
+  const int wpb = (int)(blockDim.x >> 5), kRingB = ring_bytes(ALGS, wpb);  // warps per block is a launch-time choice
   float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kSlots * 32 * kRowWords);
   int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingB) + warp * 32;
-  uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingB + kWarpsPerBlock * 32 * 8) + warp * 32;
-  float *const s_lo = reinterpret_cast<float *>(smem_raw + kRingB + kWarpsPerBlock * 32 * (8 + 4)) + warp * (32 * kRowWords);  // MODE 1 only
-  const uint64_t u = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * 32 + lane;
+  uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingB + wpb * 32 * 8) + warp * 32;
+  float *const s_lo = reinterpret_cast<float *>(smem_raw + kRingB + wpb * 32 * (8 + 4)) + warp * (32 * kRowWords);  // MODE 1 only
+  const uint64_t u = ((uint64_t)blockIdx.x * wpb + warp) * 32 + lane;
   const bool have = u < b.n_units;
 
   // ---- per-lane unit description
@@ -483,14 +485,31 @@ template <uint32_t ALGS, int MODE>
 cudaError_t launch_mode(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_series_score *scores,
                         uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                         const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, cudaStream_t st) {
-  const uint64_t per_block = kWarpsPerBlock * 32;
-  const unsigned grid = (unsigned)((b.n_units + per_block - 1) / per_block);
-  if (grid == 0) return cudaSuccess;
-  constexpr int smem = ring_bytes(ALGS) + kWarpsPerBlock * 32 * (8 + 4) + (MODE == 1 ? kLoBytes : 0);
-  cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (b.n_units == 0) return cudaSuccess;
+  // Block size against the tail effect: 8-warp blocks sit two to an SM, 6-warp blocks three (18
+  // resident warps instead of 16), so a batch that needs a second, mostly empty wave with the one
+  // may fit the first wave of the other (80 k series: 0.143 -> 0.119 ms).  Large batches keep 8
+  // warps, which measured 4-7 % faster on the HBM-bound single-algorithm passes.
+  int sm_count = 148, dev = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+  const uint64_t n_warps = (b.n_units + 31) / 32;
+  auto smem_of = [](int wpb) { return ring_bytes(ALGS, wpb) + wpb * 32 * (8 + 4) + (MODE == 1 ? lo_bytes(wpb) : 0); };
+  auto cost = [&](int wpb, uint64_t *waves_out) {  // waves x warps resident per SM (~96 registers per thread)
+    const uint64_t per_sm = std::max<uint64_t>(1, std::min<uint64_t>((227u * 1024u) / (smem_of(wpb) + 1024), 65536u / (96u * 32u * wpb)));
+    const uint64_t blocks = (n_warps + wpb - 1) / wpb, waves = (blocks + sm_count * per_sm - 1) / (sm_count * per_sm);
+    if (waves_out) *waves_out = waves;
+    return waves * per_sm * wpb;
+  };
+  uint64_t w8 = 0;
+  const uint64_t c8 = cost(8, &w8), c6 = cost(6, nullptr);
+  const int wpb = (w8 <= 4 && c6 < c8) ? 6 : 8;
+  const unsigned grid = (unsigned)((n_warps + wpb - 1) / wpb);
+  const int smem = smem_of(wpb);
+  cudaError_t e = cudaFuncSetAttribute(k_band<ALGS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       smem_of(kWarpsPerBlock));
   if (e != cudaSuccess) return e;
-  k_band<ALGS, MODE><<<grid, kWarpsPerBlock * 32, smem, st>>>(b, dp, rank_ran, scores, unit_status, unit_points,
-                                                                    band_up, band_lo, emit_off, emit_idx, emit_val);
+  k_band<ALGS, MODE><<<grid, wpb * 32, smem, st>>>(b, dp, rank_ran, scores, unit_status, unit_points, band_up, band_lo,
+                                                   emit_off, emit_idx, emit_val);
   return cudaGetLastError();
 }
 
