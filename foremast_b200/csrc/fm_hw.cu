@@ -19,28 +19,21 @@
 // fp64 throughout; the scan re-associates the sums, so floats match the sequential oracle to
 // ~1e-15 relative (tested at 1e-5), not bit for bit.
 // Algorithmic bytes per unit: 4*(n_model + n_cur) + 8 + 12 + 32.
+// This kernel serves the periods that are not multiples of 32 (and FOREMAST_GPU_HW_SMEM=1, for
+// tests); the others go to fm_hw_tm.cu, which keeps the seasonals in tensor memory.  The per-unit
+// gate, the scan and the result bookkeeping are shared (fm_hw_common.cuh).
 #include <cstdlib>
 
-#include "fm_common.cuh"
+#include "fm_hw_common.cuh"
 
 namespace {
 
 constexpr int kWarpsPerBlock = 4;
 
-struct V2 { double l, b; };
+using fm_hw::V2;
+using fm_hw::matvec;
 
-__device__ __forceinline__ V2 matvec(const double *m, V2 v) {  // m = {a00, a01, a10, a11}
-  V2 r;
-  r.l = fma(m[0], v.l, m[1] * v.b);
-  r.b = fma(m[2], v.l, m[3] * v.b);
-  return r;
-}
-
-// MODE 0 score, 1 score + bands, 2 emit pass of the anomaly list (see fm_band.cu),
-// MODE 3 fit: run the model window only and save (level, trend, sigma, phase, seasonals) per unit,
-// MODE 4 resume: load that state, score the current segment from it and save the advanced state --
-// the continuous-mode model cache (the brain's MAX_CACHE_SIZE, foremast-brain/README.md:30; jobs
-// re-armed every cycle with START_TIME/END_TIME, foremast-service/cmd/manager/main.go:59-63).
+// MODE: see fm_hw_common.cuh.
 template <int MODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const DevParams *__restrict__ dp,
                                                             fm_series_score *__restrict__ scores,
@@ -66,49 +59,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
 
   for (uint64_t u = (uint64_t)blockIdx.x * kWarpsPerBlock + warp; u < b.n_units;
        u += (uint64_t)gridDim.x * kWarpsPerBlock) {
-    const int64_t off = b.offsets[u];
-    const uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
-    uint32_t a0 = 0, ns = 0;
-    if (nh >= dp->min_historical && nh > 0) { a0 = 0; ns = nh; }
-    else if (nb >= dp->min_historical && nb > 0) { a0 = nh; ns = nb; }
-    double *const ust = (FIT || RESUME) ? state + u * (uint64_t)(m + 4) : nullptr;  // {l, b, sigma, phase | -1, S[m]}
-    if (FIT) {
-      if ((uint64_t)ns < 2ull * m) {
-        if (lane == 0) ust[3] = -1.0;  // no model for this unit
-        continue;
-      }
-    } else if (RESUME) {
-      const bool ok = nc > 0 && ust[3] >= 0.0;
-      if (!ok) {
-        if (lane == 0) {
-          fm_series_score *o = scores + u;
-#pragma unroll
-          for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
-          o->status = FM_S_UNKNOWN;
-          o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
-          unit_status[u] = FM_S_UNKNOWN;
-          unit_points[u] = 0;
-        }
-        continue;
-      }
-      ns = 0;
-    } else if (ns == 0 || nc == 0 || (uint64_t)ns < 2ull * m) {
-      continue;  // unknown unit, or not two seasons of model window
-    }
-    unsigned long long emit_base = 0;
-    if (EMIT) {
-      emit_base = emit_off[u];
-      if (emit_off[u + 1] == emit_base) continue;
-    }
-    const uint32_t c0 = nh + nb, n_stream = FIT ? ns : ns + nc;
-    const float *unit = b.values + off;
-    auto sample = [&](uint32_t q) -> float { return unit[q < ns ? a0 + q : c0 + (q - ns)]; };
-
-    uint32_t st = (FIT || RESUME) ? 0u : scores[u].status;
-    const DevRule &dr = dp->rules[b.metric_type[u] < FM_MAX_METRIC_TYPES ? b.metric_type[u] : 0];
-    const double kk = (st & FM_S_DIFFERS) ? dr.threshold * dp->differ_scale : dr.threshold;
-    const double mlb = dr.min_lower_bound;
-    const uint32_t bound = dr.bound;
+    fm_hw::Unit w;
+    if (!fm_hw::unit_begin<MODE>(b, dp, u, lane, m, scores, unit_status, unit_points, emit_off, state, w)) continue;
+    const int64_t off = w.off;
+    const uint32_t a0 = w.a0, ns = w.ns, c0 = w.c0, n_stream = w.n_stream, bound = w.bound;
+    const float *const unit = w.unit;
+    double *const ust = w.ust;
+    const double kk = w.kk, mlb = w.mlb;
+    auto sample = [&](uint32_t q) -> float { return *w.at(q); };
 
     V2 carry;
     double sse = 0.0, sigma = 0.0;
@@ -203,30 +161,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
           uo.b = fma(ab, w, uo.b);
         }
       }
-      // inclusive scan of the chunk maps v -> A^k v + u
-      V2 inc = uo;
-#pragma unroll
-      for (int i = 0; i < 5; ++i) {
-        const int o = 1 << i;
-        V2 p;
-        p.l = __shfl_up_sync(0xffffffffu, inc.l, o);
-        p.b = __shfl_up_sync(0xffffffffu, inc.b, o);
-        if ((int)lane >= o) {
-          const V2 t = matvec(Apow + 4 * i, p);
-          // inc covers the last min(o, lane+1)... chunks ending at this lane: shift the earlier block through them
-          inc.l += t.l;
-          inc.b += t.b;
-        }
-      }
-      V2 vin;  // state entering this lane's chunk
-      vin.l = __shfl_up_sync(0xffffffffu, inc.l, 1);
-      vin.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
-      if (lane == 0) { vin.l = 0.0; vin.b = 0.0; }
-      {
-        const V2 cv = matvec(Alane, carry);
-        vin.l += cv.l;
-        vin.b += cv.b;
-      }
+      // the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
+      const V2 vin = fm_hw::scan_chunks(uo, carry, Apow, Alane, lane);
       // pass 2: the real recurrence over the chunk; flags collected in a 64-bit mask (k <= 64)
       double l = vin.l, bb = vin.b;
       unsigned long long fmask = 0ull;
@@ -317,37 +253,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
         carry.l = __shfl_sync(0xffffffffu, l, src);
         carry.b = __shfl_sync(0xffffffffu, bb, src);
       }
-      if (tile_has_cur) {
-        const uint32_t cnt = __popcll(fmask);
-        uint32_t pre = cnt;  // exclusive prefix of flag counts over lanes (chunks are in stream order)
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t t = __shfl_up_sync(0xffffffffu, pre, o);
-          if ((int)lane >= o) pre += t;
-        }
-        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
-        pre -= cnt;
-        if (total) {
-          const unsigned has = __ballot_sync(0xffffffffu, cnt != 0);
-          if (n_anom == 0) {
-            const int src = __ffs(has) - 1;
-            const uint32_t cand = qa + (uint32_t)(__ffsll((long long)fmask) - 1) - ns;
-            first = __shfl_sync(0xffffffffu, cand, src);
-          }
-          if (EMIT) {
-            unsigned long long mk = fmask;
-            uint32_t r = 0;
-            while (mk) {
-              const int bit = __ffsll((long long)mk) - 1;
-              mk &= mk - 1;
-              const unsigned long long at = emit_base + n_anom + pre + r++;
-              emit_idx[at] = qa + bit - ns;
-              emit_val[at] = X[p0 + bit];
-            }
-          }
-          n_anom += total;
-        }
-      }
+      if (tile_has_cur) fm_hw::tile_flags<EMIT>(fmask, lane, qa, ns, w.emit_base, emit_idx, emit_val, X + p0, n_anom, first);
     }
     if (FIT || RESUME) {  // save the model: state after the last sample, residual sigma, phase, seasonals
       if (FIT && !sigma_ready) {
@@ -358,32 +264,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_hw(DevBatch b, const De
       }
       __syncwarp();
       for (uint32_t i = lane; i < m; i += 32) ust[4 + i] = S[i];
-      if (lane == 0) {
-        ust[0] = carry.l;
-        ust[1] = carry.b;
-        ust[2] = sigma;
-        ust[3] = (double)((phase + n_stream) % m);
-      }
+      if (lane == 0) fm_hw::save_state_scalars(ust, carry, sigma, phase, n_stream, m);
       __syncwarp();
     }
-    if (lane == 0 && !EMIT && !FIT) {
-      fm_series_score *o = scores + u;
-      if (RESUME) {
-#pragma unroll
-        for (int a = 0; a < FM_N_ALG; ++a) o->first_idx[a] = FM_NONE_IDX;
-        o->p_mw = 1.0; o->p_w = 1.0; o->p_k = 1.0;
-        o->k_eff = kk;
-        unit_points[u] = 0;
-      }
-      st |= 1u << (FM_S_ALG_SHIFT + 4);
-      if (n_anom > 0 && n_anom >= dp->min_anomaly_points) st |= FM_S_ANOMALY;
-      o->status = st;
-      o->n_anom[4] = n_anom;
-      o->first_idx[4] = first;
-      o->sigma[4] = sigma;
-      unit_status[u] = st;
-      unit_points[u] = max(unit_points[u], n_anom);
-    }
+    if (lane == 0 && !EMIT && !FIT) fm_hw::unit_finish<MODE>(dp, u, w, n_anom, first, sigma, scores, unit_status, unit_points);
   }
 }
 
