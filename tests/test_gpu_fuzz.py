@@ -1,5 +1,5 @@
 """Randomised differential test: ragged hand-built batches with awkward segment lengths (0, 1, around
-the 32-sample staging chunk, around the 1024 / 2048 sort capacities), random parameters, heavy
+the 32-sample staging chunk, around the sort capacities of the rank kernels), random parameters, heavy
 ties -- CUDA path (through the C ABI) against the oracle, same bar as test_gpu_parity.py."""
 import numpy as np
 import pytest
@@ -9,8 +9,16 @@ from tests.test_gpu_parity import assert_scores_equal
 
 pytestmark = pytest.mark.gpu
 
-LENS = [0, 1, 2, 5, 9, 10, 11, 19, 20, 21, 31, 32, 33, 63, 64, 65, 100, 127, 128, 129, 255, 256, 257, 500,
-        511, 512, 513, 720, 1000, 1023, 1024, 1025, 1440, 2047, 2048]
+import os
+
+# segment lengths around the staging chunk (32) and around every sort size of the rank kernels
+# (32*R slots, R = 2^q or 3*2^q)
+LENS = [0, 1, 2, 5, 9, 10, 11, 19, 20, 21, 31, 32, 33, 63, 64, 65, 95, 96, 97, 100, 127, 128, 129, 191, 192, 193,
+        255, 256, 257, 383, 384, 385, 500, 511, 512, 513, 720, 767, 768, 769, 1000, 1023, 1024, 1025, 1440, 1535,
+        1536, 1537, 2047, 2048]
+MAX_SEGS = [64, 300, 1024, 2048, 192, 768, 1536]
+N_UNITS = [400, 300, 200, 120, 300, 200, 150]
+SEEDS = int(os.environ.get("FOREMAST_FUZZ_SEEDS", "140"))  # 420 were run clean while developing
 
 
 def make_units(rng, n, max_seg):
@@ -41,13 +49,13 @@ def make_units(rng, n, max_seg):
     return units, mts
 
 
-@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("seed", range(SEEDS))
 def test_random_batches_against_oracle(seed):
     from foremast_b200.api import Context
     from oracle import oracle
     rng = np.random.default_rng(1000 + seed)
-    max_seg = [64, 300, 1024, 2048][seed % 4]
-    n = [400, 300, 200, 120][seed % 4]
+    max_seg = MAX_SEGS[seed % 7]
+    n = N_UNITS[seed % 7]
     units, mts = make_units(rng, n, max_seg)
     sid = np.sort(rng.integers(0, max(1, n // 7), n))
     p = oracle.params_default()
