@@ -254,6 +254,19 @@ def run_ours(args):
         nbytes = n4 * (4 * 10_140 + 52)
         other["cfg4_holt_winters_10080pt_period1440"] = {"units": n4, "ms": ms, "series_per_s": n4 / (ms * 1e-3),
                                                          "achieved_gbs": nbytes / (ms * 1e-3) / 1e9, "frac": nbytes / (ms * 1e-3) / 1e9 / peak_gbs}
+        # cfg0: the reference's own CPU-runnable case -- one canary job, 5 series, 60 vs 30 points, MA band + MWU:
+        # a latency figure (launch-bound), through the one-shot host call
+        rng = np.random.default_rng(0)
+        units0 = [([], rng.normal(100, 5, 60).astype(np.float32), rng.normal(100, 5, 30).astype(np.float32)) for _ in range(5)]
+        h0 = abi.HostCsr.from_units(units0, service_id=[0] * 5, metric_type=[1, 3, 6, 4, 5])
+        q = bench_params(default_params()); q.algorithms = abi.ALG_MA_ALL; q.pairwise = abi.PW_MANN_WHITE
+        for _ in range(20):
+            ctx.score_host(h0, q, 1)
+        t0 = time.perf_counter()
+        for _ in range(200):
+            ctx.score_host(h0, q, 1)
+        other["cfg0_single_canary_job_5_series"] = {"us_per_call": (time.perf_counter() - t0) / 200 * 1e6,
+                                                    "note": "fm_score_host, launch-latency bound; 5 launches + pool allocations + one D2H"}
 
     # ---- end to end through the public one-shot call: pinned host CSR -> H2D -> score -> verdicts D2H
     host = batch.download()
@@ -348,7 +361,7 @@ def run_ours(args):
             # per step: k_rank (Wilcoxon), k_rank (MWU/Kruskal), k_rank_finalize, k_band, k_verdict_reduce,
             # k_verdict_finalize; the e2e call runs the first five once per ~256 MiB upload chunk
             "gpu_launches": 6 * args.steps + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 3 * 8 * 2 + 1
-            + (10 * 3 + 5 * 4 + 2 if other else 0),
+            + (10 * 3 + 5 * 4 + 2 + 220 * 5 if other else 0),  # cfg2, cfg4, their generators, cfg0's 220 calls
             "clocks": clocks,
             "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
                                 "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
