@@ -278,7 +278,7 @@ static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t pe
                              uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                              const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
                              cudaStream_t st, double *state = nullptr) {
-  if (fm_hw_tm_supported(period) && !getenv("FOREMAST_GPU_HW_SMEM"))  // seasonals in tensor memory: 20 units per SM instead of 12
+  if (fm_hw_tm_supported(period) && !getenv("FOREMAST_GPU_HW_SMEM"))  // seasonals in tensor memory: 18 units per SM instead of 12
     return fm_launch_hw_tm(MODE, b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx,
                            emit_val, state, sm_count, st);
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
