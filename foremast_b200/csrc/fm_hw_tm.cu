@@ -12,7 +12,9 @@
 // one CTA of 20 warps per SM runs 20 units at a time instead of 12.  Seasonals move between tensor
 // memory and registers eight at a time (16 columns), so the inner loops also lose their per-sample
 // LDS/STS and all of k_hw's wrap-around index handling (storage is indexed by the position inside
-// the lane's chunk, never by the absolute slot).
+// the lane's chunk, never by the absolute slot).  Seasons arrive by TMA: one cp.async.bulk per season
+// into one of two buffers with an mbarrier each (4-byte cp.async when source or size is not 16 B
+// aligned), the next season in flight while this one is scored.
 // Used when period % 32 == 0; other periods take k_hw.
 #include <algorithm>
 
@@ -54,6 +56,34 @@ __device__ __forceinline__ void tm_st8(uint32_t taddr, const double (&d)[8]) {
 
 __device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
 
+// ---- TMA: one 1-D bulk copy (cp.async.bulk, UBLKCP) brings a whole season into shared memory and
+//      signals an mbarrier, instead of 45 four-byte cp.async per lane; needs 16 B aligned source and size
+__device__ __forceinline__ void mbar_init(uint64_t *bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_load(float *dst, const float *src, uint32_t bytes, uint64_t *bar) {
+  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar), d = (uint32_t)__cvta_generic_to_shared(dst);
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // earlier generic reads of dst come first
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(d),
+               "l"(src), "r"(bytes), "r"(b)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(b),
+      "r"(parity)
+      : "memory");
+}
+
 // MODE as in fm_hw.cu: 0 score, 1 score + bands, 2 emit pass of the anomaly list, 3 fit (model
 // window only, state saved), 4 resume (score the current segment from the saved state, advance it).
 template <int MODE>
@@ -69,6 +99,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   extern __shared__ float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
   __shared__ uint32_t s_tm_base;
   __shared__ double s_apow[5 * 4];
+  __shared__ __align__(8) uint64_t s_bar[kMaxWarps][2];  // one mbarrier per warp per sample buffer
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
   const uint32_t m = dp->period, k = m / 32, kb = (k + 7) / 8;  // kb blocks of eight seasonals per lane
   float *const Xb = s_x + (size_t)warp * 2 * m;
@@ -82,6 +113,11 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
   }
   if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_pow[threadIdx.x];
+  if (lane == 0) {
+    mbar_init(&s_bar[warp][0]);
+    mbar_init(&s_bar[warp][1]);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
   asm volatile("tcgen05.fence::before_thread_sync;\n");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;\n");
@@ -97,6 +133,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   const double Alane[4] = {dp->hw_lane[4 * lane], dp->hw_lane[4 * lane + 1], dp->hw_lane[4 * lane + 2],
                            dp->hw_lane[4 * lane + 3]};  // A^(k*lane)
   const uint32_t p0 = lane * k;  // this lane's chunk inside a season-long super-tile
+  uint32_t par = 0, bulk = 0;    // per sample buffer: mbarrier phase to wait for next / filled by a bulk copy
 
   for (uint64_t u = (uint64_t)blockIdx.x * n_warps + warp; u < b.n_units; u += (uint64_t)gridDim.x * n_warps) {
     fm_hw::Unit w;
@@ -107,12 +144,19 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     double *const ust = w.ust;
     const double kk = w.kk, mlb = w.mlb;
 
-    // 4-byte async copies of stream positions [q0s, q0s + m) into one of the two sample buffers, all
-    // in flight together (segments are only 4 B aligned in general); completion is awaited later
-    auto stage = [&](uint32_t q0s, float *dst) {
+    // Stream positions [q0s, q0s + m) into sample buffer `buf`: one TMA bulk copy when source and
+    // size are 16 B aligned (the usual case: model window = history, whole seasons), else 4-byte
+    // async copies, all in flight together.  Completion is awaited later (wait_buf).
+    auto stage = [&](uint32_t q0s, uint32_t buf) {
+      float *const dst = Xb + buf * m;
       const uint32_t nv = min(m, n_stream - q0s);
       if (q0s + nv <= ns || q0s >= ns) {  // one segment: one contiguous source
         const float *src = unit + (q0s < ns ? a0 + q0s : c0 + (q0s - ns));
+        if (((reinterpret_cast<uintptr_t>(src) & 15u) | (nv & 3u)) == 0) {
+          if (lane == 0) bulk_load(dst, src, nv * 4u, &s_bar[warp][buf]);
+          bulk |= 1u << buf;
+          return;
+        }
 #pragma unroll 9
         for (uint32_t i = lane; i < nv; i += 32) cp_async4(dst + i, src + i);
       } else {
@@ -122,6 +166,16 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
       }
       cp_async_commit();
+      bulk &= ~(1u << buf);
+    };
+    auto wait_buf = [&](uint32_t buf) {
+      if (bulk & (1u << buf)) {
+        mbar_wait(&s_bar[warp][buf], (par >> buf) & 1u);
+        par ^= 1u << buf;
+      } else {
+        cp_async_wait<0>();
+      }
+      __syncwarp();
     };
 
     V2 carry;
@@ -129,9 +183,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     bool sigma_ready = false;
     uint32_t phase = 0;  // seasonal slot of stream position 0
     uint32_t cur = 0;  // buffer that holds (or is receiving) the super-tile at q0
+    bool landed = false;
     __syncwarp();      // the previous unit is done with both buffers
     if (RESUME) {
-      stage(0, Xb);
+      stage(0, 0);
       carry.l = ust[0];
       carry.b = ust[1];
       sigma = ust[2];
@@ -149,10 +204,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     } else {
       // ---- initialisation from the first two seasons (D5); both lie inside the model window.  The
       //      second one is also the first super-tile scored below, so it stays where it lands.
-      stage(0, Xb);
-      stage(m, Xb + m);
-      cp_async_wait<1>();
-      __syncwarp();
+      stage(0, 0);
+      stage(m, 1);
+      wait_buf(0);
       double s0 = 0.0, s1 = 0.0;
       for (uint32_t i = lane; i < m; i += 32) s0 += (double)Xb[i];
 #pragma unroll
@@ -167,8 +221,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
         tm_st8(tS + 16 * blk, s);
       }
-      cp_async_wait<0>();
-      __syncwarp();
+      wait_buf(1);
       for (uint32_t i = lane; i < m; i += 32) s1 += (double)Xb[m + i];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
@@ -176,15 +229,16 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       carry.l = L0;
       carry.b = (M2 - L0) / (double)m;
       cur = 1;
+      landed = true;  // the loop's first super-tile is already in its buffer
     }
     tm_wait_st();
     uint32_t n_anom = 0, first = FM_NONE_IDX;
 
     for (uint32_t q0 = RESUME ? 0u : m; q0 < n_stream; q0 += m, cur ^= 1u) {
-      // this super-tile has landed and every lane is done with the other buffer: start the next one
-      cp_async_wait<0>();
-      __syncwarp();
-      if (q0 + m < n_stream) stage(q0 + m, Xb + (cur ^ 1u) * m);
+      // wait for this super-tile; every lane is then done with the other buffer: start the next one
+      if (landed) { landed = false; __syncwarp(); }
+      else wait_buf(cur);
+      if (q0 + m < n_stream) stage(q0 + m, cur ^ 1u);
       const uint32_t qa = q0 + p0;                                      // stream position of the chunk
       const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
       const float *const xp = Xb + cur * m + p0;
