@@ -224,7 +224,9 @@ void fm_host_free(fm_ctx *ctx, void *p);
  * One pass, no allocation: series[i] describes result i (byte span of its "metric" label object in
  * `json`, first timestamp, step, and the slice values[first_value .. first_value+n_values)).
  * With too small buffers it returns FM_E_RANGE and the required counts in n_series / n_values
- * (call once with caps 0 to size).  Host code only. */
+ * (call once with caps 0 to size).  Host code only, and reentrant (no shared state, no context):
+ * a worker parses one response per thread -- a response is one query of one job, so a scoring
+ * cycle has thousands of them. */
 typedef struct fm_prom_series {
   uint64_t metric_off, metric_len;
   double t0, step;

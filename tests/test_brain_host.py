@@ -103,6 +103,33 @@ def test_native_matrix_scanner_matches_json_module():
             brain.parse_matrix(bad)
 
 
+def test_native_matrix_scanner_is_reentrant():
+    """One response per thread (the worker's fan-out): same results as serially, and the calls really
+    run side by side (ctypes drops the GIL)."""
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+    rng = np.random.default_rng(5)
+    docs = []
+    for d in range(16):
+        result = [{"metric": {"pod": f"p{d}-{i}", "le": "0.5"},
+                   "values": [[1550000000 + 60 * t, repr(float(v))] for t, v in enumerate(rng.normal(100, 7, 1440))]}
+                  for i in range(8)]
+        docs.append(json.dumps({"status": "success", "data": {"resultType": "matrix", "result": result}}).encode())
+    t0 = time.perf_counter()
+    serial = [brain.parse_matrix_native(d) for d in docs]
+    t_serial = time.perf_counter() - t0
+    with ThreadPoolExecutor(8) as ex:
+        t0 = time.perf_counter()
+        threaded = list(ex.map(brain.parse_matrix_native, docs))
+        t_threads = time.perf_counter() - t0
+    for a, b in zip(serial, threaded):
+        assert len(a) == len(b) == 8
+        for (la, ta, va), (lb, tb, vb) in zip(a, b):
+            assert la == lb and ta == tb and va.tobytes() == vb.tobytes()
+    mb = sum(len(d) for d in docs) / 1e6
+    print(f"{mb:.1f} MB: serial {mb / t_serial:.0f} MB/s, 8 threads {mb / t_threads:.0f} MB/s")
+
+
 def test_exporter_series_names_match_dashboard():
     """foremast-dashboard/src/config/metrics.js:20-31 names; _anomaly value = unix ts (metricReducer.js:79-80)."""
     from foremast_b200 import exporter
