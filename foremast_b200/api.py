@@ -131,10 +131,14 @@ class Context:
         self._check(self._L.fm_model_fit(self._h, history_batch._h, C.byref(params), C.byref(h)))
         return Model(self, h)
 
-    def score_host(self, csr, params, n_services=None):
-        """One-shot host-in / host-out call (fm_score_host): returns VERDICT array."""
+    def score_host(self, csr, params, n_services=None, out=None):
+        """One-shot host-in / host-out call (fm_score_host): returns VERDICT array (`out` as in
+        Result.verdicts)."""
         ns = csr.n_services if n_services is None else n_services
-        out = np.zeros(ns, dtype=abi.VERDICT)
+        if out is None:
+            out = np.zeros(ns, dtype=abi.VERDICT)
+        assert out.dtype == abi.VERDICT and out.size >= ns and out.flags.c_contiguous
+        out = out[:ns]
         st = csr.as_struct()
         self._check(self._L.fm_score_host(self._h, C.byref(st), C.byref(params), ns, out.ctypes.data))
         return out
@@ -210,9 +214,14 @@ class Result:
     def sync(self):
         self.ctx._check(self.ctx._L.fm_result_sync(self._h))
 
-    def verdicts(self):
+    def verdicts(self, out=None):
+        """Per-service verdict records.  `out`: a caller-owned VERDICT array to fill instead of a fresh
+        one -- a view of pinned memory (Context.host_alloc) makes the download one DMA."""
         ns = self.batch.info()["n_services"]
-        out = np.zeros(ns, dtype=abi.VERDICT)
+        if out is None:
+            out = np.zeros(ns, dtype=abi.VERDICT)
+        assert out.dtype == abi.VERDICT and out.size >= ns and out.flags.c_contiguous
+        out = out[:ns]
         n = C.c_uint64()
         self.ctx._check(self.ctx._L.fm_result_verdicts(self._h, out.ctypes.data, ns, C.byref(n)))
         return out
