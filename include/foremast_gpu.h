@@ -247,7 +247,9 @@ int fm_batch_add_series(fm_batch *b, const fm_series_meta *meta,
                         const float *cur, uint32_t n_cur);
 /* Pads, uploads (H2D) and freezes the batch. */
 int fm_batch_seal(fm_batch *b);
-/* Bulk ingest of a host CSR; copied (and re-aligned if needed) during the call. */
+/* Bulk ingest of a host CSR; copied (and re-aligned if needed) during the call.  The bulk paths
+ * (this one, fm_batch_from_device, fm_score_host) take `values` as they are: the packer passes
+ * finite samples only, i.e. it has already dropped the gaps that fm_batch_add_series drops. */
 int fm_batch_from_csr(fm_ctx *ctx, const fm_csr *host_csr, fm_batch **out);
 /* Wrap a CSR that already lives in this device's HBM (borrowed until fm_batch_free). */
 int fm_batch_from_device(fm_ctx *ctx, const fm_csr *device_csr, fm_batch **out);
