@@ -56,6 +56,13 @@ struct Scan {
     p = r.ptr;
     return true;
   }
+  bool skip_number() {  // a JSON number, not converted
+    ws();
+    const char *q = p;
+    while (p < end && ((*p >= '0' && *p <= '9') || *p == '.' || *p == '-' || *p == '+' || *p == 'e' || *p == 'E')) ++p;
+    if (p == q) return ok = false;
+    return true;
+  }
   void skip_value() {  // any JSON value
     ws();
     if (p >= end) { ok = false; return; }
@@ -78,11 +85,46 @@ struct Scan {
 
 bool key_is(const char *s, size_t n, const char *lit) { return n == strlen(lit) && memcmp(s, lit, n) == 0; }
 
+// Exact fast path for the short decimals most samples are ("1", "0.25", "153.7"): up to 15
+// significant digits and a power of ten within 10^22 are both exact doubles, so one multiplication
+// or division rounds once -- the same value from_chars returns (Clinger's observation).  Anything
+// else (17-digit shortest-round-trip floats, exponents, NaN/Inf) goes to from_chars below.
+bool small_decimal(const char *s, size_t n, double *out) {
+  static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+  size_t i = 0;
+  bool neg = false;
+  if (i < n && (s[i] == '-' || s[i] == '+')) neg = s[i++] == '-';
+  uint64_t mant = 0;
+  int digits = 0, frac = 0;
+  bool seen_point = false, any = false;
+  for (; i < n; ++i) {
+    const char c = s[i];
+    if (c >= '0' && c <= '9') {
+      any = true;
+      if (mant || c != '0') {
+        if (++digits > 15) return false;
+        mant = mant * 10 + (uint64_t)(c - '0');
+      }
+      if (seen_point) ++frac;
+    } else if (c == '.' && !seen_point) {
+      seen_point = true;
+    } else {
+      return false;  // exponent, NaN, Inf, garbage
+    }
+  }
+  if (!any || frac > 22) return false;
+  const double v = (double)mant / kPow10[frac];
+  *out = neg ? -v : v;
+  return true;
+}
+
 double sample_value(const char *s, size_t n) {
   while (n && (*s == ' ')) { ++s; --n; }
+  double v;
+  if (small_decimal(s, n, &v)) return v;
   const bool plus = n && *s == '+';
   if (plus) { ++s; --n; }
-  double v;
   auto r = std::from_chars(s, s + n, v);
   if (r.ec == std::errc() && r.ptr == s + n) return v;
   return std::numeric_limits<double>::quiet_NaN();  // unparsable sample = gap
@@ -132,10 +174,12 @@ extern "C" int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_pro
                 double t_prev = 0.0;
                 while (sc.ok) {
                   if (sc.eat(']')) break;
-                  double ts;
+                  double ts = 0.0;
                   const char *vs; size_t vn;
-                  if (!sc.eat('[') || !sc.number(&ts) || !sc.eat(',') || !sc.string(&vs, &vn) || !sc.eat(']'))
-                    return finish(FM_E_INVALID);
+                  if (!sc.eat('[')) return finish(FM_E_INVALID);
+                  // only the first two timestamps carry information (t0 and the step); the rest are skipped
+                  if (cur.n_values < 2 ? !sc.number(&ts) : !sc.skip_number()) return finish(FM_E_INVALID);
+                  if (!sc.eat(',') || !sc.string(&vs, &vn) || !sc.eat(']')) return finish(FM_E_INVALID);
                   if (cur.n_values == 0) cur.t0 = ts;
                   else if (cur.n_values == 1) cur.step = ts - t_prev;
                   t_prev = ts;
