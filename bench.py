@@ -31,18 +31,27 @@ METRIC = "series-windows scored/sec (1440-pt)"
 UNIT = "series-windows/s"
 N_BASE, N_CUR, N_HIST = 720, 720, 0
 UNITS_PER_SERVICE = 80
-ALGS = abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES
+ALGS = abi.ALG_MA_ALL | abi.ALG_MA_ROLLING | abi.ALG_EWMA | abi.ALG_DES
+ALGS_R1 = abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES  # round 1's three-band step, kept under "kernels" for continuity
 
 
-def workload_name(n_units):
-    return (f"{n_units} series-windows/GPU x 1440 pt (720 baseline + 720 current), all scorers: "
-            "MWU+Wilcoxon+Kruskal (ALL), MA+EWMA+DES bands, verdict fold (80 series/service)")
+def workload_name(n_units, reference_sample=None):
+    s = (f"{n_units} series-windows/GPU x 1440 pt (720 baseline + 720 current, concurrent windows), all scorers: "
+         "MWU+Wilcoxon+Kruskal (ALL), MA_ALL+MA_ROLLING(W=30)+EWMA+DES bands, verdict fold (80 series/service); "
+         "rules: documented table for 5xx/4xx/latency/cpu/memory, (5, upper) for tps/gc/threads")
+    if reference_sample:
+        s += f"; reference arm: {reference_sample}-unit sample of it per step"
+    return s
 
 
-def bench_params(defaults):
+def bench_params(defaults, algorithms=ALGS):
+    """The deployment's rule table: the five documented rows (foremast-brain.yaml:34-73) plus one row for
+    each of the three further metric types the 8-metric synthetic services carry."""
     p = defaults
-    p.algorithms = ALGS
+    p.algorithms = algorithms
     p.pairwise = abi.PW_ALL
+    for mt in (abi.MT_TPS, abi.MT_GC, abi.MT_THREADS):
+        p.rules[mt].threshold, p.rules[mt].min_lower_bound, p.rules[mt].bound = 5.0, 0.0, abi.BOUND_UPPER
     return p
 
 
@@ -120,6 +129,24 @@ def cpu_port_rate(oracle, csr, params, threads):
     return csr.n_units / sc_t, sc_t
 
 
+INT_FIELDS = ["status", "n_anom", "first_idx", "w_n", "mw_2u1", "mw_2r1", "mw_ties", "w_2wplus", "w_2wminus", "w_ties"]
+FLT_FIELDS = ["p_mw", "p_w", "p_k", "kw_h", "k_eff", "ma_mean", "ma_std", "sigma"]
+REL_TOL = 1e-5  # north_star: smoothed values, bands and p-values within 1e-5 relative
+
+
+def compare_scores(got, ref):
+    """(#integer-field mismatches, worst relative error over the float fields) of two SERIES_SCORE arrays."""
+    int_mis = sum(int(np.count_nonzero(got[f] != ref[f])) for f in INT_FIELDS)
+    worst = 0.0
+    for f in FLT_FIELDS:
+        a, b = got[f].astype(np.float64), ref[f].astype(np.float64)
+        err = np.abs(a - b) / np.maximum(np.abs(b), 1e-300)
+        err[a == b] = 0.0
+        if err.size:
+            worst = max(worst, float(np.nanmax(err)))
+    return int_mis, worst
+
+
 def run_reference(args):
     """Reference arm: the CPU restatement of the brain's pass (oracle 'port'; the reference's own
     scorer source is not in the mount) on all host threads, same workload shape, bounded sample."""
@@ -143,7 +170,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(1_000_000), "sample_units_per_step": sample},
+            "config": {"workload": workload_name(1_000_000, reference_sample=sample), "sample_units_per_step": sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{sample} units of the same workload per step, OpenMP over units"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -181,7 +208,7 @@ def run_ours(args):
     vbuf, vbuf_ptr = ctx.host_alloc(total_services * abi.VERDICT.itemsize)
     vout = vbuf.view(abi.VERDICT)
 
-    def step(record):
+    def step(record, keep_series=False):
         res = ctx.score(batch, p)
         if world > 1:
             res.sync()
@@ -192,8 +219,9 @@ def run_ours(args):
         if record:
             for k, t in res.timings_ms().items():
                 stage_ms[k].append(t)
+        series = res.series() if keep_series else None
         res.free()
-        return v
+        return (v, series) if keep_series else v
 
     for _ in range(args.warmup):
         step(False)
@@ -208,12 +236,17 @@ def run_ours(args):
     dev_ms = ctx.timer_stop()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    # one more pass, untimed, whose per-unit scores come back for the full-size parity check below
+    verdicts, gpu_series = step(False, keep_series=True)
     verdicts = verdicts.copy()  # out of the pinned buffer the later legs reuse
+    differs_units = int(((gpu_series["status"] & abi.S_DIFFERS) != 0).sum())
+    anom_units = int(((gpu_series["status"] & abi.S_ANOMALY) != 0).sum())
 
     # ---- per-scorer passes (north_star: "each scoring kernel" against the HBM roofline): the band
     #      kernel with ONE algorithm enabled and no rank tests, same batch, timed by its own events
     single_ms = {}
-    for name, alg in (("band_ma_all", abi.ALG_MA_ALL), ("band_ewma", abi.ALG_EWMA), ("band_des", abi.ALG_DES)):
+    for name, alg in (("band_ma_all", abi.ALG_MA_ALL), ("band_ma_rolling", abi.ALG_MA_ROLLING), ("band_ewma", abi.ALG_EWMA),
+                      ("band_des", abi.ALG_DES), ("band_r1_three", ALGS_R1)):
         q = bench_params(default_params())
         q.algorithms, q.pairwise = alg, abi.PW_NONE
         ts = []
@@ -299,13 +332,46 @@ def run_ours(args):
     barrier()
     e2e_s = (time.perf_counter() - t1) / e2e_steps
     clocks = sampler.stop() if rank == 0 else None
-    if world == 1:
-        assert v2.tobytes() == verdicts.tobytes(), "e2e verdicts differ from the device-resident run"
+    # the services that lie wholly inside this rank's shard: there the merged verdicts, the one-shot call's
+    # (un-merged) verdicts and the oracle fold of the shard must all be the same bytes
+    s_lo, s_hi = -(-(rank * n) // UNITS_PER_SERVICE), ((rank + 1) * n) // UNITS_PER_SERVICE
+    e2e_equal = v2[s_lo:s_hi].tobytes() == verdicts[s_lo:s_hi].tobytes()
 
-    t = torch.tensor([dev_ms, wall_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    # ---- full-size parity (north_star Target): EVERY unit of this rank's shard against the CPU oracle --
+    #      integers and verdict records bit for bit, floats within 1e-5 -- on every rank.  At N = 1 the same
+    #      oracle pass is the cpu_baseline timing.
+    from oracle import oracle
+    threads = max(1, host_threads() // world)
+    n_par = min(n, args.parity_units)
+    stride = int(host.offsets[1])
+    sub = host if n_par == n else abi.HostCsr(host.values[:n_par * stride + 32], host.offsets[:n_par + 1], host.seg_lens[:n_par],
+                                              host.service_id[:n_par], host.metric_type[:n_par])
+    t_cpu = time.perf_counter()
+    ref, _, _ = oracle.score(sub, p, threads=threads)
+    cpu_s = time.perf_counter() - t_cpu
+    cpu_rate = n_par / cpu_s
+    int_mis, worst_rel = compare_scores(gpu_series[:n_par], ref)
+    if n_par == n:
+        v_ref = oracle.verdicts(host, ref, total_services, first_unit=rank * n)
+        verdict_equal = v_ref[s_lo:s_hi].tobytes() == verdicts[s_lo:s_hi].tobytes()
+        services_checked = s_hi - s_lo
+    else:
+        verdict_equal, services_checked = True, 0
+    del ref, gpu_series
+
+    t = torch.tensor([dev_ms, wall_ms, e2e_s * 1e3, worst_rel, float(not verdict_equal), float(not e2e_equal)],
+                     dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([int_mis, n_par, services_checked], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, wall_ms, e2e_ms = (float(x) for x in t.tolist())
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    dev_ms, wall_ms, e2e_ms, worst_rel, verdict_bad, e2e_bad = (float(x) for x in t.tolist())
+    int_mis, units_checked, services_checked = (int(x) for x in cnt.tolist())
+    parity = {"units_checked": units_checked, "int_mismatches": int_mis, "max_float_rel_err": worst_rel,
+              "float_tolerance": REL_TOL, "verdict_bytes_equal": verdict_bad == 0.0, "services_checked": services_checked,
+              "e2e_verdicts_equal_device_run": e2e_bad == 0.0,
+              "how": "every rank: oracle port over its whole shard vs fm_result_series / merged fm_result_verdicts"}
+    parity_ok = int_mis == 0 and worst_rel <= REL_TOL and verdict_bad == 0.0 and e2e_bad == 0.0
 
     if rank == 0:
         ms_per_step = dev_ms / args.steps
@@ -330,15 +396,11 @@ def run_ours(args):
                 traffic = per_unit * n if per_unit else None  # DRAM bytes per launch, from the committed ncu capture
             except Exception:
                 traffic = None
-        # CPU baseline: the oracle port on this box's host cores, bounded sample of the same workload
-        from oracle import oracle
-        threads = host_threads()
-        sample = min(n, args.cpu_units)
-        stride = int(host.offsets[1])
-        sub = abi.HostCsr(host.values[:sample * stride + 32], host.offsets[:sample + 1], host.seg_lens[:sample],
-                          host.service_id[:sample], host.metric_type[:sample])
-        # the CPU baseline is a single-GPU-run figure (rank 0, N = 1): the other ranks' host work would distort it
-        cpu_rate, cpu_s = cpu_port_rate(oracle, sub, p, threads) if world == 1 else (None, 0.0)
+        # CPU baseline = the parity pass above (the oracle port on this box's host cores over rank 0's shard);
+        # a single-GPU-run figure (rank 0, N = 1): at N > 1 the ranks share the host cores
+        sample = n_par
+        if world > 1:
+            cpu_rate = None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -357,8 +419,9 @@ def run_ours(args):
                                   "this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None},
             "kernels": kernels,
             "other_configs": other,
+            "parity": parity,
             "cpu_baseline": ({"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
-                              "sample": f"first {sample} units of rank 0's batch, one pass, {cpu_s:.2f} s"}
+                              "sample": f"first {sample} units of rank 0's batch (the parity pass), one pass, {cpu_s:.2f} s"}
                              if cpu_rate is not None else None),
             "e2e": {"value": n * world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps},
@@ -368,7 +431,9 @@ def run_ours(args):
             + (10 * 3 + 5 * 4 + 2 + 220 * 5 if other else 0),  # cfg2, cfg4, their generators, cfg0's 220 calls
             "clocks": clocks,
             "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
-                                "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum())},
+                                "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum()),
+                                "health": int((verdicts["verdict"] == abi.V_HEALTH).sum()),
+                                "units_differs_rank0": differs_units, "units_anomalous_rank0": anom_units},
         }
         OUT.emit(json.dumps(line))
     del host_p
@@ -379,6 +444,9 @@ def run_ours(args):
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    if not parity_ok:
+        sys.stderr.write(f"PARITY FAILED: {parity}\n")
+        sys.exit(1)
 
 
 class QuietStdout:
@@ -407,7 +475,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--units", type=int, default=1_000_000, help="series-windows per GPU")
-    ap.add_argument("--cpu-units", type=int, default=1_000_000, help="cpu_baseline sample (units; ~5 s on 16 cores)")
+    ap.add_argument("--parity-units", type=int, default=1_000_000_000,
+                    help="units per rank checked against the oracle (default: the whole shard; it is also the cpu_baseline sample)")
     ap.add_argument("--ref-units", type=int, default=65536, help="--impl reference: units per step")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--hw-units", type=int, default=1_000_000, help="cfg4 Holt-Winters units (10080 points each)")

@@ -391,9 +391,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         long long acc = 0, tt = 0;
         if (!any_tie) {
           // tie-free |d|: the rank of sorted position e is e+1
-          int a32 = 0;
-#pragma unroll
-          int npos = 0;
+          int a32 = 0, npos = 0;
 #pragma unroll
           for (int r = 0; r < R; ++r)
             if (r < rem && !(key[r] & 1u)) { a32 += 2 * (r + 1); ++npos; }

@@ -42,26 +42,43 @@ __device__ __forceinline__ void unit_lens(const fm_synth_config &cfg, uint64_t g
         }
     }
     if (s.v[0] % 1000u == 7u) lens[2] = 0;
+    // a whole service whose new pods have not reported yet: no current window in any of its series
+    const uint64_t svc = gu / cfg.units_per_service;
+    U4 w = philox4x32_10((uint32_t)svc, (uint32_t)(svc >> 32), 2u, 0xAu, cfg.seed, 0x466F7265u);
+    if (w.v[0] % 500u == 3u) lens[2] = 0;
   }
 }
 
+__device__ __forceinline__ float irwin_hall(const U4 &q) {
+  return (((u01(q.v[0]) + u01(q.v[1])) + (u01(q.v[2]) + u01(q.v[3]))) - 2.0f) * 1.7320508f;
+}
+
+// t = unit time of the sample; baseline and current windows are CONCURRENT (old and new pods of one
+// deployment over the same minutes): a current sample shares t -- season, drift, the load-driven noise
+// term -- with the baseline sample beside it and adds a smaller pod-private term.
 __device__ __forceinline__ float sample(const fm_synth_config &cfg, uint64_t gu, uint32_t mt, const U4 &r,
                                         uint32_t t, bool in_cur, uint32_t cur_idx) {
   float base_m = kBase[mt], sigma_m = kSigma[mt];
   float phi = u01(r.v[0]);
   float drift = (u01(r.v[1]) - 0.5f) * base_m * 1.0e-5f;
   U4 q = philox4x32_10((uint32_t)gu, (uint32_t)(gu >> 32), t, 0xBu, cfg.seed, 0x466F7265u);
-  float noise = (((u01(q.v[0]) + u01(q.v[1])) + (u01(q.v[2]) + u01(q.v[3]))) - 2.0f) * 1.7320508f;
-  noise = fminf(1.25f, fmaxf(-1.25f, noise));  /* bounded noise: k >= 2 bands stay quiet without an injected anomaly */
+  float noise = irwin_hall(q);
+  if (in_cur) {
+    U4 w = philox4x32_10((uint32_t)gu, (uint32_t)(gu >> 32), t, 0xCu, cfg.seed, 0x466F7265u);
+    noise = noise + 0.25f * irwin_hall(w);
+  }
+  noise = fminf(1.25f, fmaxf(-1.25f, noise));  /* bounded noise: k >= 3 bands stay quiet without an injected anomaly */
   float ph = (float)(t % 1440u) * (1.0f / 1440.0f) + phi;
   ph = ph - floorf(ph);
   float tri = 1.0f - 4.0f * fabsf(ph - 0.5f);
   float season = base_m * (1.0f + 0.02f * tri);
   float x = season + drift * (float)t;
   x = x + sigma_m * noise;
+  if (mt == FM_MT_ERROR5XX) x = 0.0f;  /* a healthy service answers no 5xx at all */
   if (in_cur && (cfg.flags & FM_SYNTH_ANOMALIES)) {
     if (r.v[2] % 400u == 0u && cfg.n_cur > 0 && cur_idx == r.v[3] % cfg.n_cur) x = x * 20.0f + 5.0f * base_m;
     if (r.v[2] % 800u == 1u) x = x * 1.5f + sigma_m;
+    if (mt == FM_MT_LATENCY && r.v[2] % 8u == 5u) x = x * 1.04f;  /* benign shift: differs, still inside the k = 10 band */
   }
   if (!(x > 0.0f)) x = 0.0f;
   if (mt == FM_MT_ERROR5XX || mt == FM_MT_ERROR4XX) x = rintf(x * 1000.0f) * 0.001f;
@@ -102,7 +119,7 @@ __global__ void __launch_bounds__(256) k_synth(fm_synth_config cfg, uint64_t str
       else if (k < lens[0] + lens[1]) x = sample(cfg, gu, mt, r, cfg.n_hist + (k - lens[0]), false, 0);
       else if (k < lens[0] + lens[1] + lens[2]) {
         uint32_t i = k - lens[0] - lens[1];
-        x = sample(cfg, gu, mt, r, cfg.n_hist + cfg.n_base + i, true, i);
+        x = sample(cfg, gu, mt, r, cfg.n_hist + i, true, i);
       }
       o[c] = x;
     }
