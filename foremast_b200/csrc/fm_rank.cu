@@ -18,10 +18,13 @@
 // aligned in general, and this kernel is issue-bound on the sort, not on HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
 #include <algorithm>
+#include <cstdlib>
+#include <type_traits>
 #include <utility>
 
 #include "fm_common.cuh"
 #include "fm_rank_merge.h"
+#include "fm_rank_search.h"
 
 namespace {
 
@@ -151,9 +154,11 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsign
 // positives carried across lanes), uniform trip counts.  Only units that HAVE ties come here, so
 // it is a compact out-of-line routine (rolled loops over shared memory) rather than unrolled
 // register code: the kernel's instruction footprint is what limits its issue rate.
+template <bool PAD>
 __device__ __noinline__ void run_pass(const uint32_t *tile, const int R, const uint32_t sh, const bool wilcoxon,
                                       const unsigned lane, const uint32_t n, uint16_t *rl, long long *ties_out,
                                       long long *acc2_out) {
+  auto fm_pidx = [](int e) { return PAD ? ::fm_pidx(e) : e; };  // PAD = false: linear tile (k_mw)
   const uint32_t base = lane * R;
   const uint32_t prevk = (base && base - 1 <= n) ? tile[fm_pidx(base - 1)] : 0xFFFFFFFFu;
   // sweep 1: last run start inside this lane, positives before it, positives in the lane
@@ -402,7 +407,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
             if (r <= rem) sB[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
           if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
           __syncwarp();
-          run_pass(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
+          run_pass<true>(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
           __syncwarp();
         }
         w_2wp = warp_sum_i64(acc);
@@ -416,7 +421,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         if (any_tie) {
           long long tt = 0, unused = 0;
           __syncwarp();
-          run_pass(dst, R, 0u, false, lane, n_valid, seg == 1 ? rlA : rlB, &tt, &unused);
+          run_pass<true>(dst, R, 0u, false, lane, n_valid, seg == 1 ? rlA : rlB, &tt, &unused);
           mw_ties += tt;  // per-lane partial of T_A + T_B, reduced below
           if (seg == 1) tie_a = true; else tie_b = true;
         }
@@ -450,6 +455,302 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
         o->mw_2r1 = pooled ? mw_2r1 : 0;
         o->mw_ties = pooled ? mw_ties : 0;
       }
+    }
+  }
+}
+
+
+// R interleaved lower bounds over a linear tile of N sorted keys in shared memory (the algorithm of
+// fm_lower_bound<N>, fm_rank_search.h).  adr[r] is the running lower bound of key[r] as a byte address in
+// the shared window; every step is one LDS at a literal offset, one compare and one predicated add per
+// key.  The loads are volatile asm so that the R independent chains stay interleaved as written (left to
+// itself the compiler ran the searches one after the other, 11 exposed shared-memory round trips each).
+template <int R, int LEN>
+struct LowerBound {
+  static __device__ __forceinline__ void run(uint32_t (&adr)[R], const uint32_t (&key)[R]) {
+    constexpr int half = LEN > 1 ? LEN / 2 : 0;  // LEN == 1: the closing comparison, offset 0, step 1
+    uint32_t v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v[r]) : "r"(adr[r]), "n"(half * 4));
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, %3;\n\t}"
+          : "+r"(adr[r]) : "r"(v[r]), "r"(key[r]), "n"(LEN > 1 ? half * 4 : 4));
+    if constexpr (LEN > 1) LowerBound<R, LEN - half>::run(adr, key);
+  }
+};
+
+// ---- Mann-Whitney / Kruskal-Wallis pass: sort the baseline, SEARCH the current samples ---------------
+// One warp per unit.  The current samples are staged raw by cp.async, turned into keys in place (id =
+// element index, lane l owns ids l*R .. l*R+R-1), and equal values among them are found exactly by the
+// write-then-read rounds of fm_rank_search.h (no sort, no atomics; the baseline's loads are in flight
+// meanwhile).  The baseline's 32*R key slots (real keys, then 0xFFFFFFFF) are then sorted in registers;
+// if it has ties, each element's index inside its run gives the tie term and the run length is left at
+// the run's first index; the sorted keys go to a LINEAR shared-memory tile with 128-bit stores.  Finally
+// every current key is located in the tile by a fixed-trip lower bound: lt = #{a < b}, eq = #{a == b}
+// (the run length; 1 when the baseline is tie-free).  A value's representative carries its whole group
+// with weight c = its multiplicity among the current samples, the other members weigh 0:
+//     S_lt += c*lt, S_eq += c*eq, X3 += c*eq*(eq+c), T_B += c^3 - c
+// Everything outside the sort runs in rolled loops over chunks of CH keys, so the kernel stays inside the
+// instruction cache and needs few registers.  Compared with sorting both samples and walking the merge:
+// no second sort (1504 min/max per lane), no merge-path walk, and the searches run on the load/store
+// pipe while other warps sort on the ALU pipe.
+// Shared memory per warp: tile u32[N+4] | current keys u32[key_words] (raw floats first; the
+// representative's id for keys that turn out to have one) | id table u16[n_slots] of the rounds, whose
+// bytes afterwards hold the per-id counters u16[N] and the baseline's run lengths u16[rl_entries].
+template <int R, int W>
+__global__ void __launch_bounds__(W * 32, R <= 24 ? 3 : 1) k_mw(DevBatch b, const DevParams *__restrict__ dp,
+                                                                fm_series_score *__restrict__ scores, const int rl_entries,
+                                                                const int key_words, const int n_slots) {
+  constexpr int N = 32 * R;
+  constexpr int kTileWords = N + 4;
+  constexpr int CH = R % 8 == 0 ? 8 : (R <= 6 ? R : 4);  // keys per chunk of the rolled loops
+  constexpr int NCH = R / CH;
+  static_assert(R % CH == 0, "chunks tile the lane's keys");
+  extern __shared__ __align__(16) uint32_t s_mw[];
+  const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
+  const int tab_words = (n_slots + 7) / 8 * 4;  // u16 slots, rounded to 16 bytes
+  uint32_t *const tile = s_mw + (size_t)warp * (kTileWords + key_words + tab_words);
+  uint32_t *const keysB = tile + kTileWords;  // key_words = the batch's longest segment rounded up to a chunk
+  uint16_t *const tabH = reinterpret_cast<uint16_t *>(keysB + key_words);
+  uint32_t *const cntW = keysB + key_words;  // once the rounds are over the table's bytes hold u16 counters per id
+  const uint16_t *const cntB = tabH;         // (incremented two to a word) ...
+  uint16_t *const rlA = tabH + N;            // ... and the run lengths of the baseline (host: n_slots >= N + rl_entries)
+  (void)rl_entries;
+  const uint32_t pairwise = dp->pairwise;
+  const bool want_mw = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_MANN_WHITE;
+  const bool want_k = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_KRUSKAL;
+  const uint32_t min_mw = dp->min_mann_white, min_k = dp->min_kruskal;
+  const uint32_t id0 = lane * R, m_slots = (uint32_t)n_slots;
+  using Mask = typename std::conditional<(R > 32), unsigned long long, uint32_t>::type;
+  auto mask_ffs = [](Mask m) { return sizeof(Mask) == 8 ? __ffsll((long long)m) : __ffs((int)m); };
+  auto load_chunk = [&](const uint32_t *src, uint32_t (&k)[CH]) {
+    if constexpr (CH % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < CH; i += 4) {
+        const uint4 q = *reinterpret_cast<const uint4 *>(src + i);
+        k[i] = q.x; k[i + 1] = q.y; k[i + 2] = q.z; k[i + 3] = q.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < CH; ++i) k[i] = src[i];
+    }
+  };
+  auto store_chunk = [&](uint32_t *dst, const uint32_t (&k)[CH]) {
+    if constexpr (CH % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < CH; i += 4) *reinterpret_cast<uint4 *>(dst + i) = make_uint4(k[i], k[i + 1], k[i + 2], k[i + 3]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < CH; ++i) dst[i] = k[i];
+    }
+  };
+
+  const uint64_t stride_units = (uint64_t)gridDim.x * W;
+  for (uint64_t u = (uint64_t)blockIdx.x * W + warp; u < b.n_units; u += stride_units) {
+    const int64_t off = b.offsets[u];
+    const uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
+    {  // pull the next round's samples towards L2 while this round works
+      const uint64_t un = u + stride_units;
+      if (un < b.n_units) {
+        const int64_t offn = b.offsets[un];
+        const uint32_t nhn = b.seg_lens[3 * un], len = b.seg_lens[3 * un + 1] + b.seg_lens[3 * un + 2];
+        const char *p = reinterpret_cast<const char *>(b.values + offn + nhn);
+        for (uint32_t byte = lane * 128; byte < len * 4 + 128; byte += 32 * 128)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
+      }
+    }
+    const float *base = b.values + off + nh, *cur = base + nb;
+    const bool fits = nb <= (uint32_t)N && nc <= (uint32_t)N && nb > 0 && nc > 0;
+    const bool run_mw = want_mw && nb >= min_mw && nc >= min_mw && fits;
+    const bool run_k = want_k && nb >= min_k && nc >= min_k && fits;
+    long long r1x2 = 0, u1x2 = 0, ties = 0;
+    if (run_mw || run_k) {  // warp-uniform
+      // ---- both samples requested: the current one raw into shared memory, the baseline into registers
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint32_t e = (uint32_t)(r * 32) + lane;
+        if (e < nc) cp_async4(keysB + e, cur + e);
+      }
+      cp_async_commit();
+      float x[R];
+      {
+        const uint32_t last = nb - 1;
+#pragma unroll
+        for (int r = 0; r < R; ++r) x[r] = __ldg(base + min((uint32_t)(r * 32) + lane, last));
+      }
+      cp_async_wait<0>();
+      __syncwarp();
+      // ---- raw samples -> keys in place; round 0 of the duplicate search: every key writes its id
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        const uint32_t idc = id0 + (uint32_t)(c * CH);
+        if (idc >= nc) break;  // ids from here on hold no sample (and may lie past the key region)
+        uint32_t k[CH];
+        load_chunk(keysB + idc, k);
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+          const bool valid = idc + i < nc;
+          k[i] = valid ? float_key(__uint_as_float(k[i])) : kKeySentinel;
+          if (valid) tabH[fm_dup_slot(k[i], 0u, m_slots)] = (uint16_t)(idc + i);
+        }
+        store_chunk(keysB + idc, k);
+      }
+      __syncwarp();
+      // ---- round 0: read.  pend / nonrep: one bit per key slot r of this lane
+      Mask pend = 0, nonrep = 0;
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        const uint32_t idc = id0 + (uint32_t)(c * CH);
+        if (idc >= nc) break;
+        uint32_t k[CH];
+        load_chunk(keysB + idc, k);
+        Mask p = 0, q = 0;
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+          if (idc + i < nc) {
+            const uint32_t v = tabH[fm_dup_slot(k[i], 0u, m_slots)];
+            if (v != idc + i) {
+              if (keysB[v] == k[i]) { q |= (Mask)1 << i; keysB[idc + i] = v; }
+              else p |= (Mask)1 << i;
+            }
+          }
+        }
+        pend |= p << (c * CH);
+        nonrep |= q << (c * CH);
+      }
+      __syncwarp();
+      // ---- further rounds for the few keys that lost their slot to a different value
+      for (uint32_t round = 1; __any_sync(0xffffffffu, pend != 0); ++round) {
+        for (Mask m = pend; m; m &= m - 1) {
+          const uint32_t id = id0 + (uint32_t)(mask_ffs(m) - 1);
+          tabH[fm_dup_slot(keysB[id], round, m_slots)] = (uint16_t)id;
+        }
+        __syncwarp();
+        for (Mask m = pend; m; m &= m - 1) {
+          const int r = mask_ffs(m) - 1;
+          const uint32_t id = id0 + (uint32_t)r, k = keysB[id];
+          const uint32_t v = tabH[fm_dup_slot(k, round, m_slots)];
+          if (v == id) pend &= ~((Mask)1 << r);
+          else if (keysB[v] == k) { pend &= ~((Mask)1 << r); nonrep |= (Mask)1 << r; keysB[id] = v; }
+        }
+        __syncwarp();
+      }
+      const bool dup_b = __any_sync(0xffffffffu, nonrep != 0);
+      if (dup_b) {  // multiplicity of every represented value: counters over the (now dead) id table
+        for (int i = lane; i < N / 2; i += 32) cntW[i] = 0u;
+        __syncwarp();
+        for (Mask m = nonrep; m; m &= m - 1) {
+          const uint32_t rep = keysB[id0 + (uint32_t)(mask_ffs(m) - 1)];
+          atomicAdd(cntW + (rep >> 1), 1u << ((rep & 1u) * 16u));
+        }
+      }
+      // ---- baseline: keys, sort, ties, linear tile
+      bool tie_a;
+      uint32_t tie_acc = 0;  // sum over this lane's elements of i*(i+1), i = index inside the run of equal keys
+      {
+        uint32_t key[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) key[r] = (uint32_t)(r * 32) + lane < nb ? float_key(x[r]) : kKeySentinel;
+        warp_bitonic_sort<R>(key, lane);
+        const int rem = (int)nb - (int)(lane * R);  // real keys in this lane's slots (may be <= 0 or >= R)
+        const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1), prv = __shfl_up_sync(0xffffffffu, key[R - 1], 1);
+        bool tie = false;
+#pragma unroll
+        for (int r = 0; r + 1 < R; ++r) tie = tie || ((key[r] == key[r + 1]) && (r + 1 < rem));
+        tie = tie || (lane < 31 && key[R - 1] == nxt && R < rem);
+        tie_a = __any_sync(0xffffffffu, tie);
+        if (tie_a) {
+          // run starts: the last one inside this lane, then the nearest one in the lanes before (max-scan)
+          int last_head = -1;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const bool head = r < rem && (r == 0 ? (lane == 0 || key[0] != prv) : key[r] != key[r - 1]);
+            if (head) last_head = (int)id0 + r;
+          }
+          int carry = last_head;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, carry, o);
+            if ((int)lane >= o) carry = max(carry, t);
+          }
+          int start = __shfl_up_sync(0xffffffffu, carry, 1);  // lane 0 never reads it: its first element is a head
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            if (r < rem) {
+              const int e = (int)id0 + r;
+              const bool head = r == 0 ? (lane == 0 || key[0] != prv) : key[r] != key[r - 1];
+              if (head) start = e;
+              const uint32_t i = (uint32_t)(e - start);
+              tie_acc += fm_tie_step(i);
+              const bool last = e + 1 == (int)nb || (r + 1 < R ? key[r + 1] != key[r] : nxt != key[R - 1]);
+              if (last) rlA[start] = (uint16_t)(i + 1u);
+            }
+          }
+        }
+        if constexpr (R % 4 == 0) {
+#pragma unroll
+          for (int r = 0; r < R; r += 4)
+            *reinterpret_cast<uint4 *>(tile + id0 + r) = make_uint4(key[r], key[r + 1], key[r + 2], key[r + 3]);
+        } else {
+#pragma unroll
+          for (int r = 0; r < R; ++r) tile[id0 + r] = key[r];
+        }
+        if (lane == 0) tile[N] = kKeySentinel;
+      }
+      __syncwarp();
+      // ---- lower bounds of CH keys at a time, weights, sums
+      const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tile);
+      uint32_t s_lt = 0, s_eq = 0;
+      long long x3 = 0, t_b = 0;
+      const bool plain = !tie_a && !dup_b;  // eq is 0 or 1 and every value of the current sample occurs once
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        const uint32_t idc = id0 + (uint32_t)(c * CH);
+        if (idc >= nc) break;
+        uint32_t k[CH], adr[CH];
+        load_chunk(keysB + idc, k);
+#pragma unroll
+        for (int i = 0; i < CH; ++i) adr[i] = tile_s;
+        LowerBound<CH, N>::run(adr, k);
+        const uint32_t skip = (uint32_t)(nonrep >> (c * CH));  // members represented by another key weigh 0
+        if (plain) {
+#pragma unroll
+          for (int i = 0; i < CH; ++i) {
+            const bool w = idc + i < nc;
+            uint32_t a;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(a) : "r"(adr[i]));
+            s_lt += w ? (adr[i] - tile_s) >> 2 : 0u;
+            s_eq += (w && a == k[i]) ? 1u : 0u;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < CH; ++i) {
+            const uint32_t pos = (adr[i] - tile_s) >> 2;
+            const bool w = idc + i < nc && !((skip >> i) & 1u);
+            const uint32_t cw = w ? (dup_b ? (uint32_t)cntB[idc + i] + 1u : 1u) : 0u;
+            const uint32_t eq = tile[pos] == k[i] ? (tie_a ? (uint32_t)rlA[pos] : 1u) : 0u;
+            s_lt += cw * pos;
+            s_eq += cw * eq;
+            x3 += (long long)((unsigned long long)(eq * (eq + cw)) * cw);
+            t_b += (long long)((unsigned long long)(cw * cw) * cw) - (long long)cw;
+          }
+        }
+      }
+      if (plain) x3 = 2ll * s_eq;
+      const long long lt_sum = warp_sum_i64((long long)s_lt), eq_sum = warp_sum_i64((long long)s_eq);
+      const long long x3_sum = warp_sum_i64(x3), tb_sum = dup_b ? warp_sum_i64(t_b) : 0;
+      const long long ta_sum = tie_a ? 3 * warp_sum_i64((long long)tie_acc) : 0;
+      fm_mw_finish((long long)nb, (long long)nc, lt_sum, eq_sum, ta_sum, tb_sum, x3_sum, &r1x2, &u1x2, &ties);
+      __syncwarp();  // tile, keys and table are rewritten by the next unit
+    }
+    if (lane == 0) {
+      fm_series_score *o = scores + u;
+      // fire-and-forget OR (the Wilcoxon launch, or the zero fill, wrote the word earlier in the stream)
+      if (run_mw || run_k) atomicOr(&o->status, (run_mw ? FM_S_MW_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u));
+      o->mw_2u1 = u1x2;
+      o->mw_2r1 = r1x2;
+      o->mw_ties = ties;
     }
   }
 }
@@ -504,7 +805,25 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool wan
   if (e != cudaSuccess) return e;
   if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, raw_cap);
   if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
-  if (want_pooled) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
+  static const bool old_walk = getenv("FOREMAST_GPU_MW_WALK") != nullptr;  // A/B switch: sort both samples + merge-path walk
+  if (want_pooled && old_walk) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
+  if (want_pooled && !old_walk) {
+    constexpr int W = R >= 48 ? 4 : (R == 32 ? 6 : 8);
+    constexpr int N = 32 * R;
+    const int rl_cap = seg_cap + 2, key_words = ((seg_cap + 7) & ~7) + 8;  // a chunk may start just below seg_cap
+    // id table of the duplicate search: as many u16 slots as fit while three blocks stay resident per SM
+    // (fewer slots -> more keys need a second round), never fewer than its later tenants need (counters +
+    // run lengths) nor than 1.25 keys' worth, and no more than 4 per key
+    const int budget = (227 * 1024 - 3 * 1024) / (3 * W) / 16 * 16 - ((N + 4) + key_words) * 4;
+    int n_slots = std::max(std::max(N + rl_cap, seg_cap + seg_cap / 4), std::min(budget / 2, 4 * seg_cap));
+    n_slots = (n_slots + 7) & ~7;
+    const int smem_mw = W * ((N + 4) + key_words + n_slots / 2) * 4;
+    e = cudaFuncSetAttribute(k_mw<R, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_mw);
+    if (e != cudaSuccess) return e;
+    uint64_t mw_blocks = (b.n_units + W - 1) / W;
+    if (mw_blocks > cap) mw_blocks = cap;
+    k_mw<R, W><<<(unsigned)mw_blocks, W * 32, smem_mw, st>>>(b, dp, scores, rl_cap, key_words, n_slots);
+  }
   k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
   return cudaGetLastError();
 }
