@@ -59,7 +59,7 @@ struct State {
 struct Lag {
   const float *unit;   // values + offset of this unit
   const float *srow;   // this lane's row in ring slot 0
-  uint32_t a0, ns, c0, W;
+  uint32_t a0, ns, c0, W, last_j;  // last_j: index of the last current point
   uint32_t lo_pos, cur_chunk, cur_off, prev_off;  // smem holds unit positions >= lo_pos; slot offsets in floats
   __device__ __forceinline__ bool at(uint32_t q, double &x) const {
     if (q < W) return false;
@@ -75,6 +75,28 @@ __device__ __forceinline__ bool outside(double x, double up, double lo, uint32_t
   return ((bound & 1u) && x > up) || ((bound & 2u) && x < lo);
 }
 
+// Lagging sample of the rolling band for chunks that lie at least one whole chunk inside their window, with
+// W <= 32: sample I of the chunk lags onto index I - W of the same row, or onto 32 + I - W of the previous
+// chunk's row, which the ring still holds.  cur_w / prev_w are those rows shifted by -W / 32 - W, so the
+// access is one warp-uniform select and one LDS at a literal offset.
+struct DeepLag {
+  const float *cur_w, *prev_w;
+  uint32_t W;
+  // i = index of the sample in its chunk = K + 4*v4, with cur_w / prev_w already advanced by 4*v4
+  template <int K>
+  __device__ __forceinline__ double at(uint32_t i) const { return (double)(i >= W ? cur_w : prev_w)[K]; }
+};
+
+template <uint32_t ALGS, int K>
+__device__ __forceinline__ void roll_advance_deep(State<ALGS> &s, double xd, const DeepLag &dl, uint32_t i) {
+  const double d = xd - s.x0;
+  s.rp1 += d;
+  s.rp2 = fma(d, d, s.rp2);
+  const double dq = dl.at<K>(i) - s.x0;
+  s.rq1 += dq;
+  s.rq2 = fma(dq, dq, s.rq2);
+}
+
 template <uint32_t ALGS>
 __device__ __forceinline__ void roll_advance(State<ALGS> &s, double xd, uint32_t q, const Lag &lag, bool valid) {
   const double d = xd - s.x0;
@@ -88,10 +110,13 @@ __device__ __forceinline__ void roll_advance(State<ALGS> &s, double xd, uint32_t
   }
 }
 
-template <uint32_t ALGS>
+template <uint32_t ALGS, bool DEEP = false, int K = 0>
 __device__ __forceinline__ void src_update(State<ALGS> &s, double xd, double alpha, double ab, uint32_t q, const Lag &lag,
-                                           bool valid) {
-  if (ALGS & FM_ALG_MA_ROLLING) roll_advance<ALGS>(s, xd, q, lag, valid);
+                                           bool valid, const DeepLag *dl = nullptr, uint32_t i = 0) {
+  if (ALGS & FM_ALG_MA_ROLLING) {
+    if (DEEP) roll_advance_deep<ALGS, K>(s, xd, *dl, i);
+    else roll_advance<ALGS>(s, xd, q, lag, valid);
+  }
   if (ALGS & FM_ALG_MA_ALL) {
     double d = xd - s.x0;
     s.s1 += d;
@@ -131,8 +156,57 @@ __device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t
 // (x < lo) || (x < mlb), which needs no fp64 max, and a disabled side is a constant-false predicate.
 struct FastRule {
   double k, nk, mlb;
+  double k2e;  // k*k*(1 - kRollEps), 0 when k is not a usable (finite, >= 0) threshold: every point then takes the exact path
   bool up_on, lo_on;
 };
+
+// ---- rolling band without a division or a square root per point ------------------------------------
+// The oracle flags a current point x against up = fma(k, sd, mean), mean = x0 + a1/c, sd = sqrt(var),
+// var = max(0, fma(-m1, m1, a2/c)) with a1, a2 the window sums of d = x - x0 and d*d: two fp64 divisions
+// and a square root per point, and the band kernel spent its time in them.  Nearly every point lies well
+// inside its band, and that can be seen from the sums alone: with D = c*(x - x0) - a1 = c*(x - mean) and
+// V = c*a2 - a1^2 = c^2*var (both exact up to rounding), x > up would need D > k*sqrt(V).  The filter
+// below proves "not flagged" whenever (|D| + eD)^2 <= k^2*(V - eV)*(1 - eps) (or D is on the harmless
+// side of a one-sided band), where eD and eV bound -- with a factor > 1000 to spare, eps = 2^-40 against
+// unit roundoff 2^-53 -- every rounding the oracle's own evaluation and this one can have made:
+//   |c*mean_o - (c*x0 + a1)| <= 2^-52 (c|x0| + |a1|),  |c^2 var_o - V| <= 2^-51 (c|a2| + a1^2),
+//   sd_o and up_o within 2^-53 relative of sqrt(var_o) and k*sd_o + mean_o.
+// Points the filter cannot clear (real anomalies, points within 1e-12 of the band edge, degenerate
+// windows) are decided by roll_exact, the oracle's arithmetic verbatim, so flags stay bit-identical.
+constexpr double kRollEps = 9.094947017729282e-13;  // 2^-40
+
+struct RollExact {
+  bool flag;
+  double sd;
+};
+__device__ __noinline__ RollExact roll_exact(double a1, double a2, uint32_t cnt, double x0, double k, double mlb,
+                                             uint32_t bound, double xd) {
+  const double m1 = a1 / (double)cnt, mean = x0 + m1;
+  double var = fma(-m1, m1, a2 / (double)cnt);
+  if (!(var > 0.0)) var = 0.0;
+  const double sd = sqrt(var), up = fma(k, sd, mean);
+  double lo = fma(-k, sd, mean);
+  lo = lo < mlb ? mlb : lo;
+  RollExact r;
+  r.flag = ((bound & 1u) && xd > up) || ((bound & 2u) && xd < lo);
+  r.sd = sd;
+  return r;
+}
+
+// true when the point certainly is NOT outside the rolling band (see above); c = window count as a double
+__device__ __forceinline__ bool roll_clear(double a1, double a2, double c, double d, double xd, double x0,
+                                           const FastRule &fr) {
+  const double D = fma(c, d, -a1);
+  const double a1sq = a1 * a1;
+  const double V = fma(c, a2, -a1sq);
+  const double eD = kRollEps * fma(c, fabs(xd) + fabs(x0), fabs(a1));
+  const double eV = kRollEps * fma(c, fabs(a2), a1sq);
+  const double kin = fr.k2e * (V - eV);
+  const double dp = D + eD, dm = eD - D;  // upper side: D + eD, lower side: -D + eD
+  const bool in_up = !fr.up_on || dp <= 0.0 || dp * dp <= kin;
+  const bool in_lo = !fr.lo_on || dm <= 0.0 || dm * dm <= kin;
+  return in_up && in_lo;
+}
 
 __device__ __forceinline__ bool outside_fast(double x, double up, double lo, const FastRule &fr) {
   return (fr.up_on && x > up) || (fr.lo_on && (x < lo || x < fr.mlb));
@@ -141,33 +215,41 @@ __device__ __forceinline__ bool outside_fast(double x, double up, double lo, con
 // Fast-path twin of cur_update for chunks that lie entirely inside the current window: identical
 // arithmetic, but flags are gathered into one bit mask per algorithm per 32-sample chunk (bit I)
 // and counted once per chunk instead of being counted point by point.
-template <uint32_t ALGS, int I>
+// K = position of the sample inside its group of four, i = its index in the chunk (the bit it owns in mask).
+template <uint32_t ALGS, int K, bool DEEP = false>
 __device__ __forceinline__ void cur_fast(State<ALGS> &s, const FastRule &fr, double xd, uint32_t j, bool valid,
-                                         double alpha, double ab, uint32_t (&mask)[4], const Lag &lag) {
+                                         double alpha, double ab, uint32_t (&mask)[4], const Lag &lag, const uint32_t i,
+                                         const DeepLag *dl = nullptr) {
   if (ALGS & FM_ALG_MA_ROLLING) {
-    const uint32_t q = lag.ns + j, cnt = lag.W < q ? lag.W : q;
+    // DEEP: at least 32 current points lie behind this one, so the window is full (W <= 32)
+    const uint32_t q = lag.ns + j, cnt = DEEP ? dl->W : (lag.W < q ? lag.W : q);
     const double a1 = s.rp1 - s.rq1, a2 = s.rp2 - s.rq2;
-    const double m1 = a1 / (double)cnt, mean = s.x0 + m1;
-    double var = fma(-m1, m1, a2 / (double)cnt);
-    if (!(var > 0.0)) var = 0.0;
-    const double sd = sqrt(var), up = fma(fr.k, sd, mean), lo = fma(fr.nk, sd, mean);
-    if (valid) s.rsd = sd;
-    if (outside_fast(xd, up, lo, fr)) mask[3] |= 1u << I;
-    roll_advance<ALGS>(s, xd, q, lag, valid);
+    const double d = xd - s.x0;
+    // the last current point also reports the sd it was judged with (sigma[1]): exact path
+    const bool need = valid && (!roll_clear(a1, a2, (double)cnt, d, xd, s.x0, fr) || j == lag.last_j);
+    bool f = fr.lo_on && xd < fr.mlb;  // the clamp of the lower band is a plain comparison
+    if (need) {
+      const RollExact e = roll_exact(a1, a2, cnt, s.x0, fr.k, fr.mlb, (fr.up_on ? 1u : 0u) | (fr.lo_on ? 2u : 0u), xd);
+      f = e.flag;
+      s.rsd = e.sd;
+    }
+    if (f) mask[3] |= 1u << i;
+    if (DEEP) roll_advance_deep<ALGS, K>(s, xd, *dl, i);
+    else roll_advance<ALGS>(s, xd, q, lag, valid);
   }
   if (ALGS & FM_ALG_MA_ALL) {
     // s.ma_lo already carries the clamp, so the plain comparison is the oracle's
-    if ((fr.up_on && xd > s.ma_up) || (fr.lo_on && xd < s.ma_lo)) mask[0] |= 1u << I;
+    if ((fr.up_on && xd > s.ma_up) || (fr.lo_on && xd < s.ma_lo)) mask[0] |= 1u << i;
   }
   if (ALGS & FM_ALG_EWMA) {
     const double f0 = s.es, up = fma(fr.k, s.esig, f0), lo = fma(fr.nk, s.esig, f0);
-    if (outside_fast(xd, up, lo, fr)) mask[1] |= 1u << I;
+    if (outside_fast(xd, up, lo, fr)) mask[1] |= 1u << i;
     const double e = xd - f0;
     s.es = fma(alpha, e, s.es);
   }
   if (ALGS & FM_ALG_DES) {
     const double f0 = s.dl + s.db, up = fma(fr.k, s.dsig, f0), lo = fma(fr.nk, s.dsig, f0);
-    if (outside_fast(xd, up, lo, fr)) mask[2] |= 1u << I;
+    if (outside_fast(xd, up, lo, fr)) mask[2] |= 1u << i;
     const double e = xd - f0;
     s.dl = fma(alpha, e, f0);
     s.db = fma(ab, e, s.db);
@@ -280,6 +362,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   }
   FastRule fr;
   fr.k = r.k; fr.nk = -r.k; fr.mlb = r.mlb;
+  fr.k2e = (r.k >= 0.0 && r.k < 1.0e150) ? r.k * r.k * (1.0 - kRollEps) : 0.0;
   fr.up_on = (r.bound & 1u) != 0; fr.lo_on = (r.bound & 2u) != 0;
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta;
   const uint32_t band_alg = BANDS ? dp->band_algorithm : 0u;
@@ -295,8 +378,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   lag.unit = b.values + off;
   lag.srow = s_ring + lane * kRowWords;
   lag.lo_pos = 0xFFFFFFFFu; lag.cur_chunk = 0; lag.cur_off = 0; lag.prev_off = 0;
-  lag.a0 = a0; lag.ns = ns; lag.c0 = c0;
+  lag.a0 = a0; lag.ns = ns; lag.c0 = c0; lag.last_j = active ? nc - 1 : 0xFFFFFFFFu;
   lag.W = active ? dp->ma_window : 0xFFFFFFFFu;  // lanes without a unit never touch memory
+  const uint32_t w_uniform = dp->ma_window;
 
   // ---- staging set-up
   s_off[lane] = off;
@@ -339,12 +423,34 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     const bool done = cs >= c1, not_started = ce <= a0;
     const bool cls_src = cs >= a0 + 2 && ce <= a1;
     const bool cls_cur = cs > c0 && ce <= c1;
+    // rolling band, W <= 32: the chunk before this one lies in the same window, so every lagging sample is
+    // in this lane's row of the current or the previous ring slot
+    const bool roll_deep = (ALGS & FM_ALG_MA_ROLLING) && w_uniform <= 32u;
+    DeepLag dlag;
+    if (ALGS & FM_ALG_MA_ROLLING) {
+      dlag.W = w_uniform;
+      dlag.cur_w = row - w_uniform;
+      dlag.prev_w = s_ring + ((ch + kSlots - 1) % kSlots) * (32 * kRowWords) + lane * kRowWords + 32 - w_uniform;
+    }
     const bool cls_skip = not_started || done || (cs >= a1 && ce <= c0);
     const bool dontcare = !active || done || not_started;
 
-    if (__all_sync(0xffffffffu, cls_src || dontcare)) {
+    if (roll_deep && __all_sync(0xffffffffu, (cls_src && cs >= a0 + 32u) || dontcare)) {
+      // rolled over the eight groups of four samples: the unrolled chunk bodies of all variants together
+      // were 11 k instructions in the four-scorer kernel and it waited on instruction fetch
+#pragma unroll 1
+      for (int v4 = 0; v4 < 8; ++v4) {
+        const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
+        const uint32_t i0 = v4 * 4;
+        src_update<ALGS, true, 0>(s, (double)x.x, alpha, ab, 0u, lag, true, &dlag, i0 + 0);
+        src_update<ALGS, true, 1>(s, (double)x.y, alpha, ab, 0u, lag, true, &dlag, i0 + 1);
+        src_update<ALGS, true, 2>(s, (double)x.z, alpha, ab, 0u, lag, true, &dlag, i0 + 2);
+        src_update<ALGS, true, 3>(s, (double)x.w, alpha, ab, 0u, lag, true, &dlag, i0 + 3);
+        dlag.cur_w += 4; dlag.prev_w += 4;
+      }
+    } else if (__all_sync(0xffffffffu, cls_src || dontcare)) {
       // whole chunk inside the model window for every lane: no range checks
-#pragma unroll
+#pragma unroll 1
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t q = cs + v4 * 4 - a0;
@@ -360,7 +466,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       // so the band arrays are written in full 128 B lines instead of 4 B at a 5.7 KB stride.
       float *uprow = s_ring + (ch % kSlots) * (32 * kRowWords) + lane * kRowWords;
       float *lorow = s_lo + lane * kRowWords;
-#pragma unroll
+#pragma unroll 1
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(uprow + v4 * 4);
         const uint32_t j = cs + v4 * 4 - c0;
@@ -384,19 +490,39 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
           *reinterpret_cast<float4 *>(band_lo + at) = *reinterpret_cast<const float4 *>(s_lo + rw * kRowWords + col4 * 4);
         }
       }
+    } else if (MODE == 0 && roll_deep && __all_sync(0xffffffffu, (cls_cur && cs >= c0 + 32u) || dontcare)) {
+      uint32_t mask[4] = {0u, 0u, 0u, 0u};
+      const uint32_t j0 = cs - c0;
+#pragma unroll 1
+      for (int v4 = 0; v4 < 8; ++v4) {
+        const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
+        const uint32_t i0 = v4 * 4;
+        cur_fast<ALGS, 0, true>(s, fr, (double)x.x, j0 + i0 + 0, cls_cur, alpha, ab, mask, lag, i0 + 0, &dlag);
+        cur_fast<ALGS, 1, true>(s, fr, (double)x.y, j0 + i0 + 1, cls_cur, alpha, ab, mask, lag, i0 + 1, &dlag);
+        cur_fast<ALGS, 2, true>(s, fr, (double)x.z, j0 + i0 + 2, cls_cur, alpha, ab, mask, lag, i0 + 2, &dlag);
+        cur_fast<ALGS, 3, true>(s, fr, (double)x.w, j0 + i0 + 3, cls_cur, alpha, ab, mask, lag, i0 + 3, &dlag);
+        dlag.cur_w += 4; dlag.prev_w += 4;
+      }
+      if (cls_cur) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+          if (mask[a]) {
+            if (s.cnt[a] == 0) s.first[a] = j0 + (uint32_t)(__ffs(mask[a]) - 1);
+            s.cnt[a] += __popc(mask[a]);
+          }
+      }
     } else if (MODE == 0 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
       uint32_t mask[4] = {0u, 0u, 0u, 0u};
       const uint32_t j0 = cs - c0;
-      auto quad = [&](auto V4) {
-        constexpr int v4 = decltype(V4)::value;
+#pragma unroll 1
+      for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
-        cur_fast<ALGS, v4 * 4 + 0>(s, fr, (double)x.x, j0 + v4 * 4 + 0, cls_cur, alpha, ab, mask, lag);
-        cur_fast<ALGS, v4 * 4 + 1>(s, fr, (double)x.y, j0 + v4 * 4 + 1, cls_cur, alpha, ab, mask, lag);
-        cur_fast<ALGS, v4 * 4 + 2>(s, fr, (double)x.z, j0 + v4 * 4 + 2, cls_cur, alpha, ab, mask, lag);
-        cur_fast<ALGS, v4 * 4 + 3>(s, fr, (double)x.w, j0 + v4 * 4 + 3, cls_cur, alpha, ab, mask, lag);
-      };
-      quad(IntC<0>{}); quad(IntC<1>{}); quad(IntC<2>{}); quad(IntC<3>{});
-      quad(IntC<4>{}); quad(IntC<5>{}); quad(IntC<6>{}); quad(IntC<7>{});
+        const uint32_t i0 = v4 * 4;
+        cur_fast<ALGS, 0>(s, fr, (double)x.x, j0 + i0 + 0, cls_cur, alpha, ab, mask, lag, i0 + 0);
+        cur_fast<ALGS, 1>(s, fr, (double)x.y, j0 + i0 + 1, cls_cur, alpha, ab, mask, lag, i0 + 1);
+        cur_fast<ALGS, 2>(s, fr, (double)x.z, j0 + i0 + 2, cls_cur, alpha, ab, mask, lag, i0 + 2);
+        cur_fast<ALGS, 3>(s, fr, (double)x.w, j0 + i0 + 3, cls_cur, alpha, ab, mask, lag, i0 + 3);
+      }
       if (cls_cur) {  // lanes that only ride along (done / not started) keep their counters
 #pragma unroll
         for (int a = 0; a < 4; ++a)

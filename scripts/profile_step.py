@@ -15,6 +15,9 @@ pairwise = int(sys.argv[7]) if len(sys.argv) > 7 else abi.PW_ALL
 with Context(0) as ctx:
     b = ctx.batch_synth(units, *shape, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
     p = default_params()
+    if os.environ.get("FM_BENCH_RULES", "1") != "0":  # the rule table of bench.py (rows for tps / gc / threads)
+        for mt in (abi.MT_TPS, abi.MT_GC, abi.MT_THREADS):
+            p.rules[mt].threshold, p.rules[mt].min_lower_bound, p.rules[mt].bound = 5.0, 0.0, abi.BOUND_UPPER
     p.algorithms = algs
     p.pairwise = pairwise
     for _ in range(passes):
