@@ -82,6 +82,7 @@ __device__ __forceinline__ bool outside(double x, double up, double lo, uint32_t
 struct DeepLag {
   const float *cur_w, *prev_w;
   uint32_t W;
+  double Wd;  // (double)W: the window is full on these paths
   // i = index of the sample in its chunk = K + 4*v4, with cur_w / prev_w already advanced by 4*v4
   template <int K>
   __device__ __forceinline__ double at(uint32_t i) const { return (double)(i >= W ? cur_w : prev_w)[K]; }
@@ -203,9 +204,9 @@ __device__ __forceinline__ bool roll_clear(double a1, double a2, double c, doubl
   const double eV = kRollEps * fma(c, fabs(a2), a1sq);
   const double kin = fr.k2e * (V - eV);
   const double dp = D + eD, dm = eD - D;  // upper side: D + eD, lower side: -D + eD
-  const bool in_up = !fr.up_on || dp <= 0.0 || dp * dp <= kin;
-  const bool in_lo = !fr.lo_on || dm <= 0.0 || dm * dm <= kin;
-  return in_up && in_lo;
+  const bool in_up = !fr.up_on | (dp <= 0.0) | (dp * dp <= kin);
+  const bool in_lo = !fr.lo_on | (dm <= 0.0) | (dm * dm <= kin);
+  return in_up & in_lo;
 }
 
 __device__ __forceinline__ bool outside_fast(double x, double up, double lo, const FastRule &fr) {
@@ -223,11 +224,13 @@ __device__ __forceinline__ void cur_fast(State<ALGS> &s, const FastRule &fr, dou
   if (ALGS & FM_ALG_MA_ROLLING) {
     // DEEP: at least 32 current points lie behind this one, so the window is full (W <= 32)
     const uint32_t q = lag.ns + j, cnt = DEEP ? dl->W : (lag.W < q ? lag.W : q);
+    const double c = DEEP ? dl->Wd : (double)cnt;
     const double a1 = s.rp1 - s.rq1, a2 = s.rp2 - s.rq2;
     const double d = xd - s.x0;
-    // the last current point also reports the sd it was judged with (sigma[1]): exact path
-    const bool need = valid && (!roll_clear(a1, a2, (double)cnt, d, xd, s.x0, fr) || j == lag.last_j);
-    bool f = fr.lo_on && xd < fr.mlb;  // the clamp of the lower band is a plain comparison
+    // the last current point also reports the sd it was judged with (sigma[1]): exact path.  Bitwise logic:
+    // the filter is evaluated by every lane, only the exact path is a branch
+    const bool need = valid & (!roll_clear(a1, a2, c, d, xd, s.x0, fr) | (j == lag.last_j));
+    bool f = fr.lo_on & (xd < fr.mlb);  // the clamp of the lower band is a plain comparison
     if (need) {
       const RollExact e = roll_exact(a1, a2, cnt, s.x0, fr.k, fr.mlb, (fr.up_on ? 1u : 0u) | (fr.lo_on ? 2u : 0u), xd);
       f = e.flag;
@@ -429,6 +432,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     DeepLag dlag;
     if (ALGS & FM_ALG_MA_ROLLING) {
       dlag.W = w_uniform;
+      dlag.Wd = (double)w_uniform;
       dlag.cur_w = row - w_uniform;
       dlag.prev_w = s_ring + ((ch + kSlots - 1) % kSlots) * (32 * kRowWords) + lane * kRowWords + 32 - w_uniform;
     }
