@@ -197,6 +197,7 @@ def run_ours(args):
 
     n = args.units
     ctx = Context(local)
+    fdist.init_library_comm(ctx, rank, world)  # the cross-GPU merge runs inside the library (fm_result_merge)
     total_services = (n * world + UNITS_PER_SERVICE - 1) // UNITS_PER_SERVICE
     batch = ctx.batch_synth(n, N_HIST, N_BASE, N_CUR, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
                             flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, first_unit=rank * n)
@@ -210,11 +211,7 @@ def run_ours(args):
 
     def step(record, keep_series=False):
         res = ctx.score(batch, p)
-        if world > 1:
-            res.sync()
-            counts, worst = fdist.alias_service_buffers(res)
-            fdist.merge_service_counters(counts, worst)
-            torch.cuda.synchronize()
+        res.merge()  # NCCL all-reduce pair on the library's stream (no-op at N = 1), no host sync
         v = res.verdicts(out=vout)  # finalize kernel + D2H of the per-service verdicts
         if record:
             for k, t in res.timings_ms().items():
@@ -335,6 +332,9 @@ def run_ours(args):
     # the services that lie wholly inside this rank's shard: there the merged verdicts, the one-shot call's
     # (un-merged) verdicts and the oracle fold of the shard must all be the same bytes
     s_lo, s_hi = -(-(rank * n) // UNITS_PER_SERVICE), ((rank + 1) * n) // UNITS_PER_SERVICE
+    v2 = v2.copy()
+    hit = v2["worst_unit"] != abi.NONE_IDX
+    v2["worst_unit"][hit] += rank * n  # the one-shot call numbers units from 0, the sharded batch from rank * n
     e2e_equal = v2[s_lo:s_hi].tobytes() == verdicts[s_lo:s_hi].tobytes()
 
     # ---- full-size parity (north_star Target): EVERY unit of this rank's shard against the CPU oracle --
@@ -373,6 +373,7 @@ def run_ours(args):
               "how": "every rank: oracle port over its whole shard vs fm_result_series / merged fm_result_verdicts"}
     parity_ok = int_mis == 0 and worst_rel <= REL_TOL and verdict_bad == 0.0 and e2e_bad == 0.0
 
+    line = None
     if rank == 0:
         ms_per_step = dev_ms / args.steps
         value = n * world / (ms_per_step * 1e-3)
@@ -409,14 +410,14 @@ def run_ours(args):
                        "l2": "inputs (5.76 GB/GPU) larger than L2; no flush needed",
                        "timing": "CUDA events on the library stream around the K steps, max over ranks",
                        "wall_ms_per_step": wall_ms / args.steps},
-            "roofline": {"bound": "hbm", "kernel": {"rank_wilcoxon": "k_rank<R,0> (Wilcoxon pass)", "rank_mw": "k_rank<R,1> (Mann-Whitney/Kruskal pass) + k_rank_finalize",
+            "roofline": {"bound": "hbm", "kernel": {"rank_wilcoxon": "k_rank<R,0> (Wilcoxon pass)", "rank_mw": "k_mw<R,W> (Mann-Whitney/Kruskal pass) + k_rank_finalize",
                                                "band": "k_band", "verdict": "k_verdict_reduce"}[dom],
                          "achieved": kernels[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                          "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
                          "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0,
-                         "note": ("the rank kernels are bound by the ALU pipe (integer min/max of the sorting network, "
-                                  "81-83 % busy in profiles/r1_final2_rank_band.md), not by HBM; the HBM-bound kernels of "
-                                  "this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None},
+                         "note": ("the rank kernels are bound by instruction issue (a register sorting network of 1504 integer "
+                                  "min/max per lane per sort, then shared-memory searches; profiles/r2_rank_mw.md), not by HBM; "
+                                  "the HBM-bound kernels of this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None},
             "kernels": kernels,
             "other_configs": other,
             "parity": parity,
@@ -435,13 +436,66 @@ def run_ours(args):
                                 "health": int((verdicts["verdict"] == abi.V_HEALTH).sum()),
                                 "units_differs_rank0": differs_units, "units_anomalous_rank0": anom_units},
         }
-        OUT.emit(json.dumps(line))
     del host_p
-    ctx.host_free(vbuf_ptr)
     for _, ptr in pins:
         ctx.host_free(ptr)
     batch.free()
+
+    # ---- cfg5 (BASELINE.json configs[4]): a 10 M-series sweep, 125 000 services of 80, sharded over the N
+    #      GPUs by service (strong scaling: 57.6 GB of samples in total, 1/N of it per GPU), all scorers,
+    #      per-service verdict merge through fm_result_merge.  Timed like the headline: CUDA events on the
+    #      library stream around K passes, barrier on both sides, max over ranks.
+    cfg5 = None
+    if args.cfg5_units > 0:
+        n5 = args.cfg5_units
+        lo, hi = fdist.shard_range(n5, rank, world, UNITS_PER_SERVICE)
+        ns5 = (n5 + UNITS_PER_SERVICE - 1) // UNITS_PER_SERVICE
+        b5 = ctx.batch_synth(hi - lo, N_HIST, N_BASE, N_CUR, units_per_service=UNITS_PER_SERVICE, n_metric_types=8,
+                             flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, first_unit=lo)
+        b5.set_shard(lo, ns5)
+        v5buf, v5ptr = ctx.host_alloc(ns5 * abi.VERDICT.itemsize)
+        v5 = v5buf.view(abi.VERDICT)
+
+        def step5():
+            r5 = ctx.score(b5, p)
+            r5.merge()
+            out = r5.verdicts(out=v5)
+            r5.free()
+            return out
+        for _ in range(2):
+            step5()
+        barrier()
+        ctx.timer_start()
+        for _ in range(args.cfg5_steps):
+            vv = step5()
+        ms5 = ctx.timer_stop() / args.cfg5_steps
+        barrier()
+        # the merge alone: K all-reduce pairs on a scratch result (its counters are garbage afterwards)
+        r5 = ctx.score(b5, p)
+        r5.sync()
+        barrier()
+        ctx.timer_start()
+        for _ in range(20):
+            r5.merge()
+        merge_us = ctx.timer_stop() / 20 * 1e3
+        r5.free()
+        t5 = torch.tensor([ms5, merge_us], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t5, op=dist.ReduceOp.MAX)
+        ms5, merge_us = (float(x) for x in t5.tolist())
+        cfg5 = {"units_total": n5, "units_this_rank": hi - lo, "n_services": ns5, "ms_per_step": ms5,
+                "series_windows_per_s": n5 / (ms5 * 1e-3), "verdict_merge_us": merge_us, "steps": args.cfg5_steps,
+                "scaling": "strong", "unhealth": int((vv["verdict"] == abi.V_UNHEALTH).sum()),
+                "unknown": int((vv["verdict"] == abi.V_UNKNOWN).sum()),
+                "note": "sharded by service with fm_batch_set_shard; merge = fm_result_merge (NCCL all-reduce pair, one group)"}
+        b5.free()
+        ctx.host_free(v5ptr)
+    ctx.host_free(vbuf_ptr)
     ctx.close()
+    if rank == 0 and line is not None:
+        if cfg5 is not None:
+            line["other_configs"]["cfg5_10M_x_1440_sharded"] = cfg5
+        OUT.emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     if not parity_ok:
@@ -481,6 +535,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--hw-units", type=int, default=1_000_000, help="cfg4 Holt-Winters units (10080 points each)")
     ap.add_argument("--skip-configs", action="store_true", help="skip the extra cfg2 / cfg4 timings")
+    ap.add_argument("--cfg5-units", type=int, default=10_000_000, help="cfg5: series of the sharded sweep in total (0 = skip)")
+    ap.add_argument("--cfg5-steps", type=int, default=3)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -35,6 +35,7 @@ MAX_METRIC_TYPES = 16
 MT_NAMES = {"error5xx": MT_ERROR5XX, "error4xx": MT_ERROR4XX, "latency": MT_LATENCY, "cpu": MT_CPU,
             "memory": MT_MEMORY, "tps": MT_TPS, "gc": MT_GC, "threads": MT_THREADS}
 
+COMM_ID_BYTES = 128
 V_HEALTH, V_UNKNOWN, V_UNHEALTH = 0, 1, 2
 # the statuses the brain writes into the ES document (foremast-service/pkg/converter/converter.go:16-21)
 V_STATUS = {V_HEALTH: "completed_health", V_UNKNOWN: "completed_unknown", V_UNHEALTH: "completed_unhealth"}

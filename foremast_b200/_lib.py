@@ -19,6 +19,7 @@ SYMBOLS = {
     "fm_version": (C.c_int, []),
     "fm_strerror": (C.c_char_p, [C.c_int]),
     "fm_last_error": (C.c_char_p, [_P]),
+    "fm_last_error_copy": (C.c_int, [_P, C.c_char_p, C.c_uint32]),
     "fm_params_default": (None, [C.POINTER(abi.Params)]),
     "fm_device_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.c_char_p, C.c_uint32]),
     "fm_timer_start": (C.c_int, [_P]),
@@ -50,6 +51,11 @@ SYMBOLS = {
     "fm_result_anomalies_unit": (C.c_int, [_P, C.c_uint64, _P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "fm_result_anomalies_all": (C.c_int, [_P, _P, _P, _P, C.c_uint64]),
     "fm_scan_counts_static": (C.c_int, [_P, C.c_uint64, _P, _P]),
+    "fm_comm_unique_id": (C.c_int, [_P, C.c_uint32]),
+    "fm_comm_init": (C.c_int, [_P, _P, C.c_int32, C.c_int32]),
+    "fm_comm_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "fm_comm_destroy": (None, [_P]),
+    "fm_result_merge": (C.c_int, [_P]),
     "fm_result_service_buffers": (C.c_int, [_P, _PP, _PP, C.POINTER(C.c_uint32)]),
     "fm_result_timings": (C.c_int, [_P, C.POINTER(C.c_float), C.c_uint32]),
     "fm_result_free": (None, [_P]),

@@ -15,6 +15,22 @@ def default_params():
     return p
 
 
+def _prefer_bundled_nccl():
+    """A Python process may import torch AFTER the library has opened NCCL; torch needs its own (newer)
+    bundled copy, and two copies with one soname cannot coexist.  So before the library's first NCCL use,
+    load the bundled copy if there is one -- the library's dlopen("libnccl.so.2") then resolves to it."""
+    import importlib.util
+    import os
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    if spec and spec.submodule_search_locations:
+        path = os.path.join(list(spec.submodule_search_locations)[0], "lib", "libnccl.so.2")
+        if os.path.exists(path):
+            C.CDLL(path, mode=C.RTLD_GLOBAL)
+
+
 def scan_counts_static(d_counts_ptr, n, d_offsets_ptr, stream=0):
     """Allocation-free exclusive scan of per-unit anomaly counts (fm_scan_counts_static): device
     uint32 counts[n] -> device uint64 offsets[n+1], on the current device and the given stream.
@@ -70,6 +86,32 @@ class Context:
         ms = C.c_float()
         self._check(self._L.fm_timer_stop(self._h, C.byref(ms)))
         return ms.value
+
+    # ---- multi-GPU merge (fm_comm_*): one context per GPU, NCCL on the library's stream
+    @staticmethod
+    def comm_unique_id():
+        """128 opaque bytes made by ONE rank and handed to all of them (fm_comm_unique_id)."""
+        L = load()
+        _prefer_bundled_nccl()
+        buf = C.create_string_buffer(abi.COMM_ID_BYTES)
+        rc = L.fm_comm_unique_id(buf, abi.COMM_ID_BYTES)
+        if rc:
+            raise ForemastGpuError(rc, L.fm_strerror(rc).decode())
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, world):
+        """Collective over all `world` contexts (fm_comm_init)."""
+        assert len(unique_id) == abi.COMM_ID_BYTES
+        _prefer_bundled_nccl()
+        self._check(self._L.fm_comm_init(self._h, unique_id, rank, world))
+
+    def comm_info(self):
+        r, w = C.c_int32(), C.c_int32()
+        self._check(self._L.fm_comm_info(self._h, C.byref(r), C.byref(w)))
+        return r.value, w.value
+
+    def comm_destroy(self):
+        self._L.fm_comm_destroy(self._h)
 
     def host_alloc(self, nbytes):
         """Pinned host memory as a uint8 numpy array (freed with host_free)."""
@@ -258,6 +300,11 @@ class Result:
         n = C.c_uint32()
         self.ctx._check(self.ctx._L.fm_result_anomalies_unit(self._h, unit, idx.ctypes.data, val.ctypes.data, cap, C.byref(n)))
         return idx[:n.value].copy(), val[:n.value].copy()
+
+    def merge(self):
+        """Cross-GPU merge of the per-service counters on the library's stream (fm_result_merge);
+        verdicts() afterwards returns the merged verdicts on every rank."""
+        self.ctx._check(self.ctx._L.fm_result_merge(self._h))
 
     def service_buffers(self):
         counts, worst, ns = C.c_void_p(), C.c_void_p(), C.c_uint32()

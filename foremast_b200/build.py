@@ -6,10 +6,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libforemast_gpu.so")
-SOURCES = ["fm_api.cu", "fm_ingest.cu", "fm_synth.cu", "fm_band.cu", "fm_rank.cu", "fm_hw.cu", "fm_hw_tm.cu", "fm_scan.cu", "fm_verdict.cu"]
+SOURCES = ["fm_api.cu", "fm_ingest.cu", "fm_synth.cu", "fm_band.cu", "fm_rank.cu", "fm_hw.cu", "fm_hw_tm.cu", "fm_scan.cu", "fm_verdict.cu", "fm_comm.cu"]
 # --fmad=false: fused multiply-adds only where the source says fma() (oracle/DECISIONS.md)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "--fmad=false",
-              "-std=c++17", "-diag-suppress=186", "-Xcompiler", "-fPIC,-O2", "-shared", "--threads", "0"]
+              "-std=c++17", "-diag-suppress=186", "-Xcompiler", "-fPIC,-O2", "-shared", "--threads", "0", "-ldl"]
 
 
 def _stale():

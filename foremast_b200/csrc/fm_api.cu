@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "fm_common.cuh"
+#include "fm_internal.h"
 
 // ------------------------------------------------------------------ objects
 
@@ -22,8 +23,10 @@ struct fm_ctx {
   cudaStream_t stream = nullptr;       // compute
   cudaStream_t copy_stream = nullptr;  // H2D staging of fm_score_host
   cudaEvent_t timer[2] = {nullptr, nullptr};
-  std::mutex mu;
+  std::mutex mu;         // GPU submission
+  std::mutex err_mu;     // last_error only: set_err may run with or without `mu` held
   std::string last_error;
+  fm_comm_state comm;    // multi-GPU merge (fm_comm.cu)
 };
 
 struct fm_batch {
@@ -77,7 +80,10 @@ struct fm_model {
 namespace {
 
 int set_err(fm_ctx *ctx, int code, const std::string &msg) {
-  if (ctx) ctx->last_error = msg;
+  if (ctx) {
+    std::lock_guard<std::mutex> g(ctx->err_mu);
+    ctx->last_error = msg;
+  }
   return code;
 }
 
@@ -217,6 +223,12 @@ void free_batch_device(fm_batch *b) {
 
 }  // namespace
 
+std::mutex &fm_ctx_mutex(fm_ctx *ctx) { return ctx->mu; }
+fm_comm_state *fm_ctx_comm(fm_ctx *ctx) { return &ctx->comm; }
+int fm_ctx_device(const fm_ctx *ctx) { return ctx->device; }
+cudaStream_t fm_ctx_stream(const fm_ctx *ctx) { return ctx->stream; }
+int fm_set_error(fm_ctx *ctx, int code, const std::string &msg) { return set_err(ctx, code, msg); }
+
 // ------------------------------------------------------------------ life cycle
 
 extern "C" {
@@ -240,7 +252,24 @@ const char *fm_strerror(int code) {
   }
 }
 
-const char *fm_last_error(const fm_ctx *ctx) { return ctx ? ctx->last_error.c_str() : "no context"; }
+// The text is copied under the error lock into a buffer of the CALLING thread, so the pointer stays valid
+// (until this thread asks again) even while other threads fail on the same context.
+const char *fm_last_error(const fm_ctx *ctx) {
+  if (!ctx) return "no context";
+  static thread_local std::string copy;
+  fm_ctx *c = const_cast<fm_ctx *>(ctx);
+  std::lock_guard<std::mutex> g(c->err_mu);
+  copy = c->last_error;
+  return copy.c_str();
+}
+
+int fm_last_error_copy(const fm_ctx *ctx, char *buf, uint32_t cap) {
+  if (!ctx || !buf || cap == 0) return FM_E_INVALID;
+  fm_ctx *c = const_cast<fm_ctx *>(ctx);
+  std::lock_guard<std::mutex> g(c->err_mu);
+  snprintf(buf, cap, "%s", c->last_error.c_str());
+  return FM_OK;
+}
 
 // Documented defaults: deploy/foremast/3_brain/foremast-brain.yaml:24-79; the rest oracle/DECISIONS.md.
 void fm_params_default(fm_params *p) {
@@ -305,6 +334,7 @@ int fm_init(const fm_config *cfg, fm_ctx **out) {
 
 void fm_shutdown(fm_ctx *ctx) {
   if (!ctx) return;
+  fm_comm_destroy(ctx);
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   for (auto &e : ctx->timer)
@@ -926,6 +956,16 @@ int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst,
   if (worst) *worst = reinterpret_cast<uint64_t *>(r->d_worst);
   if (n_services) *n_services = r->n_services;
   return FM_OK;
+}
+
+// Cross-GPU merge of the per-service counters, in place, ordered on the context's stream between the
+// scoring kernels and the finalize pass of fm_result_verdicts: no host synchronisation in between.
+int fm_result_merge(fm_result *r) {
+  if (!r) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  return fm_comm_merge_counters(ctx, r->d_counts, r->d_worst, r->n_services);
 }
 
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap) {

@@ -1,8 +1,10 @@
 """Multi-GPU plumbing: one process per GPU, series sharded by contiguous unit ranges snapped to
 service boundaries, and the single exchange step of the path -- the merge of the dense
-per-service counters -- as two torch.distributed all-reduces (NCCL on GPUs, gloo in
-the CPU tests).  The reference scales the same way, with shared-nothing brain pods
-(docs/guides/design.md:37-41); it has no collective at all.
+per-service counters.  On GPUs the merge lives behind the C ABI (fm_comm_init /
+fm_result_merge: NCCL on the library's own stream); this module only carries the 128-byte NCCL id to
+the ranks (`init_library_comm`) and keeps the host-side twin of the merge -- two torch.distributed
+all-reduces -- that the CPU tests run over gloo.  The reference scales the same way, with
+shared-nothing brain pods (docs/guides/design.md:37-41); it has no collective at all.
 """
 import numpy as np
 
@@ -32,9 +34,24 @@ def alias_service_buffers(result):
     return counts, worst
 
 
+def init_library_comm(ctx, rank, world, group=None):
+    """Creates the library's NCCL communicator on `ctx` (one context per rank): rank 0 makes the id,
+    torch.distributed (any backend) carries its 128 bytes to the other ranks."""
+    import torch.distributed as dist
+    from .api import Context
+    if world == 1:
+        return
+    box = [Context.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    ctx.comm_init(box[0], rank, world)
+
+
 def merge_service_counters(counts, worst, group=None):
     """In-place merge across ranks: counters add, worst-unit keys max.  Keys are
-    (points << 32 | ~unit) < 2^63, so a signed 64-bit max is exact."""
+    (points << 32 | ~unit) < 2^63, so a signed 64-bit max is exact.  Host-side twin of
+    fm_result_merge.  With tensors that alias a result's device buffers the caller owns the ordering:
+    result.sync() before this call (the library writes them on its private stream) and a device
+    synchronise after it, before result.verdicts()."""
     import torch.distributed as dist
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return counts, worst

@@ -202,8 +202,11 @@ int fm_init(const fm_config *cfg, fm_ctx **out);
 void fm_shutdown(fm_ctx *ctx);
 int fm_version(void);
 const char *fm_strerror(int code);
-/* Text of the last failure on this context ("reason" of elasticsearchstore.go:94-98). */
+/* Text of the last failure on this context ("reason" of elasticsearchstore.go:94-98).  Safe while other
+ * threads use the context: fm_last_error returns a copy that belongs to the calling thread (valid until
+ * that thread calls it again); fm_last_error_copy writes into the caller's buffer (what a cgo shim uses). */
 const char *fm_last_error(const fm_ctx *ctx);
+int fm_last_error_copy(const fm_ctx *ctx, char *buf, uint32_t cap);
 /* Documented defaults of foremast-brain.yaml:24-79 + oracle/DECISIONS.md. */
 void fm_params_default(fm_params *p);
 int fm_device_info(const fm_ctx *ctx, int32_t *sm_count, uint64_t *hbm_bytes, char *name, uint32_t name_cap);
@@ -332,7 +335,34 @@ int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, 
 #define FM_SCAN_STATIC_MAX_COUNTS 16777216ull
 int fm_scan_counts_static(const uint32_t *d_counts, uint64_t n, uint64_t *d_offsets, void *cuda_stream);
 
-/* Device pointers of the dense per-service counters, for the cross-GPU merge:
+/* ---------------------------------------------------------------- multi-GPU merge
+ *
+ * The reference scales with shared-nothing brain pods that only meet in Elasticsearch
+ * (docs/guides/design.md:37-41).  Here every GPU scores its shard of the series (one context per GPU, in
+ * one process or many) and the dense per-service counters are merged by one NCCL all-reduce pair
+ * (u32[4S] summed, u64[S] maxed, one launch) that is ordered on the context's own stream:
+ *
+ *     rank 0: fm_comm_unique_id(id)  -> hand the 128 bytes to every rank (the host's own channel)
+ *     all   : fm_comm_init(ctx, id, rank, world)            -- collective, once per context
+ *     sweep : fm_batch_set_shard(b, first_unit, n_services_total); fm_score(ctx, b, p, &r);
+ *             fm_result_merge(r);                            -- collective, asynchronous, no host sync
+ *             fm_result_verdicts(r, ...)                     -- every rank gets the merged verdicts
+ *
+ * NCCL is loaded at run time (libnccl.so.2); a host that never calls fm_comm_* does not need it.
+ * Failures return FM_E_COMM with the NCCL text in fm_last_error. */
+#define FM_COMM_ID_BYTES 128
+int fm_comm_unique_id(void *id_out, uint32_t cap);
+int fm_comm_init(fm_ctx *ctx, const void *unique_id, int32_t rank, int32_t world);
+int fm_comm_info(const fm_ctx *ctx, int32_t *rank, int32_t *world);
+void fm_comm_destroy(fm_ctx *ctx); /* also done by fm_shutdown */
+/* In-place merge of this result's per-service counters across the ranks of the context's communicator
+ * (a no-op without one).  Call it on every rank, in the same order of results. */
+int fm_result_merge(fm_result *r);
+
+/* Device pointers of the dense per-service counters, for hosts that merge them by other means.  They are
+ * written by fm_score on the context's PRIVATE non-blocking stream and read again, on that same stream, by
+ * fm_result_verdicts: a caller that touches them on another stream must call fm_result_sync first and must
+ * finish (synchronise) its own work on them before calling fm_result_verdicts.
  * counts = uint32[4*n_services] (n_units, n_unknown, n_anom_units, n_anom_points), summed;
  * worst  = uint64[n_services]   ((points << 32) | ~unit), maxed. */
 int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst, uint32_t *n_services);

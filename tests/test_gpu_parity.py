@@ -507,3 +507,71 @@ def test_full_size_properties(ctx, oracle):
     assert_scores_equal(sc[idx], ref)
     res.free()
     b.free()
+
+
+def test_library_comm_single_rank_merge_is_identity(ctx, oracle):
+    """fm_comm_init with a world of one (loads NCCL, builds a communicator) and fm_result_merge: the merged
+    verdicts of a single shard are its own verdicts."""
+    from foremast_b200.api import Context
+    c2 = Context()
+    try:
+        c2.comm_init(Context.comm_unique_id(), 0, 1)
+        assert c2.comm_info() == (0, 1)
+        b = c2.batch_synth(1000, 64, 40, 40, units_per_service=7, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+        p = full_params(oracle)
+        res = c2.score(b, p)
+        res.merge()
+        got = res.verdicts()
+        host = b.download()
+        ref, _, _ = oracle.score(host, p)
+        assert got.tobytes() == oracle.verdicts(host, ref, b.info()["n_services"]).tobytes()
+        res.free()
+        b.free()
+    finally:
+        c2.close()
+
+
+def test_library_comm_two_gpus_merge_matches_oracle_fold(oracle):
+    """Two contexts on two devices of one process, one thread each: shard by service, fm_result_merge through
+    the C ABI (NCCL on the library's streams), merged verdicts on BOTH ranks = the oracle fold of the whole."""
+    import threading
+    from foremast_b200 import dist as fdist
+    from foremast_b200._lib import ForemastGpuError
+    from foremast_b200.api import Context
+    try:
+        Context(1).close()
+    except ForemastGpuError:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    n, ups, world = 4001, 7, 2
+    whole = oracle.synth(n, 64, 40, 40, units_per_service=ups, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES)
+    p = full_params(oracle)
+    ref, _, _ = oracle.score(whole, p)
+    want = oracle.verdicts(whole, ref, whole.n_services)
+    uid = Context.comm_unique_id()
+    out, errs = [None] * world, []
+
+    def run(rank):
+        try:
+            c = Context(rank)
+            c.comm_init(uid, rank, world)
+            lo, hi = fdist.shard_range(n, rank, world, ups)
+            b = c.batch_synth(hi - lo, 64, 40, 40, units_per_service=ups, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES,
+                              first_unit=lo)
+            b.set_shard(lo, whole.n_services)
+            res = c.score(b, p)
+            res.merge()
+            out[rank] = res.verdicts().copy()
+            res.free()
+            b.free()
+            c.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    assert not errs, errs
+    for r in range(world):
+        assert out[r] is not None and out[r].tobytes() == want.tobytes()
