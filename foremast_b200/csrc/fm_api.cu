@@ -177,7 +177,10 @@ int upload_aligned(fm_batch *b, const fm_csr *h, uint64_t used) {
   cudaStream_t st = ctx->stream;
   if (used) FM_CUDA(ctx, cudaMemcpyAsync(b->d_values, h->values, used * sizeof(float), cudaMemcpyHostToDevice, st));
   FM_CUDA(ctx, cudaMemsetAsync(b->d_values + used, 0, 32 * sizeof(float), st));
-  FM_CUDA(ctx, cudaMemcpyAsync(b->d_offsets, h->offsets, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  if (n && h->offsets)
+    FM_CUDA(ctx, cudaMemcpyAsync(b->d_offsets, h->offsets, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  else  // an empty batch may come without arrays: its one offset is 0
+    FM_CUDA(ctx, cudaMemsetAsync(b->d_offsets, 0, sizeof(int64_t), st));
   if (n) {
     FM_CUDA(ctx, cudaMemcpyAsync(b->d_seg, h->seg_lens, 3 * n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     if (h->service_id)
@@ -441,7 +444,7 @@ int fm_batch_seal(fm_batch *b) {
   fm_ctx *ctx = b->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
-  b->h_offsets.push_back((int64_t)b->h_values.size());
+  b->h_offsets.push_back((int64_t)b->h_values.size());  // the end offset; taken back if the upload fails
   fm_csr h;
   h.n_units = b->h_sid.size();
   h.values = b->h_values.data();
@@ -452,9 +455,12 @@ int fm_batch_seal(fm_batch *b) {
   bool aligned;
   uint64_t used;
   int rc = scan_host_csr(ctx, &h, &aligned, &used, b);
-  if (rc) return rc;
-  rc = upload_aligned(b, &h, used);
-  if (rc) { free_batch_device(b); return rc; }
+  if (rc == FM_OK) rc = upload_aligned(b, &h, used);
+  if (rc) {  // the batch stays open and consistent: a retry, or more add_series calls, start from a clean CSR
+    free_batch_device(b);
+    b->h_offsets.pop_back();
+    return rc;
+  }
   b->sealed = true;
   std::vector<float>().swap(b->h_values);
   return FM_OK;
@@ -691,7 +697,7 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
   uint32_t *ustat = r->d_unit_status + i0, *upts = r->d_unit_points + i0;
   if (timed) FM_R(cudaEventRecord(r->ev[1], st));
   if (do_rank)
-    FM_R(fm_launch_rank(db, r->d_params, p->pairwise, std::max(b->max_base, b->max_cur), scores, ctx->sm_count, st,
+    FM_R(fm_launch_rank(db, r->d_params, p->pairwise, b->max_base, b->max_cur, scores, ctx->sm_count, st,
                         timed ? r->ev[2] : nullptr));
   else if (timed)
     FM_R(cudaEventRecord(r->ev[2], st));
@@ -714,8 +720,6 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
 static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
   int rc = validate_params(ctx, p);
   if (rc) return rc;
-  if (p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0 && std::max(b->max_base, b->max_cur) > 2048)
-    return set_err(ctx, FM_E_UNSUPPORTED, "rank tests support baseline/current segments of at most 2048 samples");
   fm_result *r = new (std::nothrow) fm_result;
   if (!r) return FM_E_NOMEM;
   rc = result_alloc(ctx, b, p, r);
@@ -1003,9 +1007,8 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
   if (rc) return rc;
   if (n_services < tb.n_services) return set_err(ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1");
   tb.n_services = n_services;
-  if (!aligned || h->n_units == 0 ||
-      (p->pairwise != FM_PW_NONE && tb.max_base > 0 && tb.max_cur > 0 && std::max(tb.max_base, tb.max_cur) > 2048)) {
-    // unaligned input has to be re-packed first (and unsupported shapes report their error): plain path
+  if (!aligned || h->n_units == 0) {
+    // unaligned input has to be re-packed first: plain path
     g.unlock();
     fm_batch *b = nullptr;
     rc = fm_batch_from_csr(ctx, h, &b);

@@ -72,7 +72,7 @@ __device__ __forceinline__ void cp_async_wait() {
 void fm_launch_synth(const fm_synth_config &cfg, uint64_t stride, float *values, int64_t *offsets,
                      uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type, cudaStream_t st);
 void fm_launch_batch_stats(const DevBatch &b, uint32_t *out6, cudaStream_t st);
-cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_seg,
+cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
                            fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon);
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,

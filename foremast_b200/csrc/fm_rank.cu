@@ -8,14 +8,13 @@
 //
 // Mapping: ONE WARP PER SERIES-WINDOW.  Each lane keeps R keys in registers (32*R >= segment
 // length); the warp sorts them with a register-resident bitonic network -- compare-exchanges
-// inside a lane are two FMNMX/VIMNMX, the 15 lane-crossing stages use SHFL.BFLY -- so the sort
-// never touches memory.  Baseline and current are sorted separately and payload-free (group
-// membership is recovered by merging, not carried through the sort); Wilcoxon sorts one u32 key
-// per pair with the sign in bit 0.  Tie runs are measured while the sorted keys are still in
-// registers (run_pass); the sorted runs then go to padded shared-memory tiles and the 32 lanes
-// split the merged order by merge path (fm_rank_merge.h), each walking an equal span with a
-// uniform trip count, to accumulate exact int64 rank sums and tie terms.  Reads are plain coalesced 4-byte loads: segment starts are not 16 B
-// aligned in general, and this kernel is issue-bound on the sort, not on HBM.
+// inside a lane are two VIMNMX, the 15 lane-crossing stages use SHFL.BFLY -- so the sort never
+// touches memory.  Two launches: k_wilcoxon sorts one u32 key per pair (|d| with the sign in bit 0)
+// and ranks it; k_mw sorts the baseline only and locates every current sample in it by a lower
+// bound over a shared-memory tile (fm_rank_search.h), so group membership never rides through a
+// sort.  Exact int64 rank sums and tie terms come out of both; k_rank_finalize turns them into
+// p-values.  Reads are plain coalesced 4-byte loads / cp.async: segment starts are not 16 B aligned
+// in general, and these kernels are bound by instruction issue, not by HBM.
 // Algorithmic bytes per unit: 4*(n_base+n_cur) + 8 + 12 + 64.
 #include <algorithm>
 #include <cstdlib>
@@ -23,12 +22,15 @@
 #include <utility>
 
 #include "fm_common.cuh"
-#include "fm_rank_merge.h"
 #include "fm_rank_search.h"
 
 namespace {
 
 constexpr int kWarpsPerBlock = 8;
+
+// shared-memory index of sorted element e in the Wilcoxon kernel's tile: one pad word per 32 keeps the
+// warp's post-sort stores (lane stride R words) spread over the banks
+__host__ __device__ __forceinline__ int fm_pidx(int e) { return e + (e >> 5); }
 constexpr uint32_t kKeySentinel = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint32_t sel_minmax(bool lower, uint32_t a, uint32_t b) { return lower ? min(a, b) : max(a, b); }
@@ -252,41 +254,30 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
   return p > 1.0 ? 1.0 : p;
 }
 
-// PHASE 0: Wilcoxon signed-rank (one sort of |d| keys).  PHASE 1: Mann-Whitney / Kruskal-Wallis
-// (baseline and current sorted separately, merge-path walk).  Two launches instead of one fused
-// kernel: each keeps its instruction footprint inside the instruction cache (the fused kernel
-// lost 4-5 issue slots per issued instruction to fetch stalls), and both are ALU-bound, so the
+// Wilcoxon signed-rank pass: one warp per unit, one sort of |d| keys (sign in bit 0).  The NEXT unit's
+// paired samples are staged in shared memory with 4-byte cp.async while the current unit is being
+// sorted in registers; tie-free units never touch the tile.  A separate launch from the Mann-Whitney
+// pass: each keeps its instruction footprint inside the instruction cache (one fused kernel lost 4-5
+// issue slots per issued instruction to fetch stalls), and both are bound by instruction issue, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
-template <int R, int PHASE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(DevBatch b, const DevParams *__restrict__ dp,
-                                                              fm_series_score *__restrict__ scores, const int tile_words,
-                                                              const int kRl) {
-  // PHASE 0 keeps the compile-time tile (one tile per warp is small anyway; a run-time size cost it
-  // registers and 18 % of its speed); PHASE 1 sizes its four tables for the batch
-  const int kTile = PHASE == 0 ? 33 * R + 2 : tile_words;
-  // kTile: padded words per sorted run (+ sentinel slot), kRl: run-length entries (u16) per run; both
-  // sized by the host for the longest segment of the batch, not for the 32*R capacity of the sort
-  extern __shared__ uint32_t s_tiles[];  // [warps][2][kTile] keys, then [warps][2][kRl] u16 run lengths
-
+template <int R>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxon(DevBatch b, const DevParams *__restrict__ dp,
+                                                                                  fm_series_score *__restrict__ scores,
+                                                                                  const int raw_cap) {
+  constexpr int kTile = 33 * R + 2;      // padded words of the sorted run (+ sentinel slot): compile-time, a run-time
+                                         // size cost this kernel registers and 18 % of its speed
+  extern __shared__ uint32_t s_tiles[];  // [warps][kTile] keys, then [warps][2][raw_cap] staged samples
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t pairwise = dp->pairwise;
-  const bool want_mw = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_MANN_WHITE;
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
-  const bool want_k = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_KRUSKAL;
-  // PHASE 0 only ever needs one tile (the tie pass of the |d| keys): a smaller footprint, more warps
-  constexpr int kTilesPerWarp = PHASE == 0 ? 1 : 2;
-  uint32_t *const sA = s_tiles + (size_t)warp * kTilesPerWarp * kTile, *const sB = PHASE == 0 ? sA : sA + kTile;
-  uint16_t *const rlA = reinterpret_cast<uint16_t *>(s_tiles + (size_t)kWarpsPerBlock * kTilesPerWarp * kTile) + (size_t)warp * 2 * kRl;
-  uint16_t *const rlB = rlA + kRl;
-  // PHASE 0 stages the NEXT unit's paired samples in shared memory with 4-byte cp.async while the
-  // current unit is being sorted in registers (kRl doubles as the per-segment capacity there)
-  float *const rawA = reinterpret_cast<float *>(s_tiles + (size_t)kWarpsPerBlock * kTilesPerWarp * kTile) + (size_t)warp * 2 * kRl;
-  float *const rawB = rawA + kRl;
+  uint32_t *const sB = s_tiles + (size_t)warp * kTile;
+  float *const rawA = reinterpret_cast<float *>(s_tiles + (size_t)kWarpsPerBlock * kTile) + (size_t)warp * 2 * raw_cap;
+  float *const rawB = rawA + raw_cap;
   auto stage_pairs = [&](uint64_t uu) {
     if (uu < b.n_units) {
       const int64_t o = b.offsets[uu];
       const uint32_t h0 = b.seg_lens[3 * uu], n1 = b.seg_lens[3 * uu + 1], n2 = b.seg_lens[3 * uu + 2];
-      const uint32_t mm = min(min(n1, n2), (uint32_t)kRl);
+      const uint32_t mm = min(min(n1, n2), (uint32_t)raw_cap);
       const float *pa = b.values + o + h0, *pb = pa + n1;
       for (uint32_t e = lane; e < mm; e += 32) {
         cp_async4(rawA + e, pa + e);
@@ -295,166 +286,88 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_rank(De
     }
     cp_async_commit();
   };
-  if (PHASE == 0) stage_pairs((uint64_t)blockIdx.x * kWarpsPerBlock + warp);
+  stage_pairs((uint64_t)blockIdx.x * kWarpsPerBlock + warp);
 
   // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
   const uint64_t n_rounds = (b.n_units + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
   for (uint64_t round = 0; round < n_rounds; ++round) {
     const uint64_t u = (round * gridDim.x + blockIdx.x) * kWarpsPerBlock + warp;
     const bool have = u < b.n_units;
-    int64_t off = 0;
-    uint32_t nh = 0, nb = 0, nc = 0;
-    if (have) {
-      off = b.offsets[u];
-      nh = b.seg_lens[3 * u]; nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2];
-    }
-    if (PHASE == 1) {  // pull the next round's samples towards L2 while this round sorts
-      const uint64_t un = u + (uint64_t)gridDim.x * kWarpsPerBlock;
-      if (un < b.n_units) {
-        const int64_t offn = b.offsets[un];
-        const uint32_t nhn = b.seg_lens[3 * un], len = b.seg_lens[3 * un + 1] + b.seg_lens[3 * un + 2];
-        const char *p = reinterpret_cast<const char *>(b.values + offn + nhn);
-        for (uint32_t byte = lane * 128; byte < len * 4 + 128; byte += 32 * 128)
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
-      }
-    }
-    const float *base = b.values + off + nh, *cur = base + nb;
-    const uint32_t m = min(nb, nc);
-    const bool fits = nb <= 32u * R && nc <= 32u * R;
-    const bool run_mw = PHASE == 1 && have && want_mw && nb >= dp->min_mann_white && nc >= dp->min_mann_white && m > 0 && fits;
-    const bool run_w = PHASE == 0 && have && want_w && m >= dp->min_wilcoxon && m > 0 && fits;
-    const bool run_k = PHASE == 1 && have && want_k && nb >= dp->min_kruskal && nc >= dp->min_kruskal && m > 0 && fits;
-    const bool pooled = run_mw || run_k;
-
-    long long w_2wp = 0, w_ties = 0, mw_2r1 = 0, mw_ties = 0;
+    uint32_t nb = 0, nc = 0;
+    if (have) { nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2]; }
+    const uint32_t m = min(nb, nc);  // the pairs are the first m samples of each segment (D8)
+    // D17: at most FM_RANK_MAX_SEGMENT pairs are ranked; the launch picks R so that every ranked unit fits
+    const bool run_w = have && want_w && m >= dp->min_wilcoxon && m > 0 && m <= 32u * R && m <= (uint32_t)FM_RANK_MAX_SEGMENT;
+    long long w_2wp = 0, w_ties = 0;
     uint32_t w_n = 0;
-    bool tie_a = false, tie_b = false;  // equal samples inside the baseline / inside the current segment
-
-    // one sort routine, three passes: |d| keys (Wilcoxon), baseline, current
-#pragma unroll 1
-    for (int seg = PHASE == 0 ? 0 : 1; seg < (PHASE == 0 ? 1 : 3); ++seg) {
-      if (PHASE == 0 && !run_w) {  // nothing to rank here, but the staging pipeline must keep moving
-        cp_async_wait<0>();
-        __syncwarp();
-        stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
-        continue;
-      }
-      if (seg == 0 ? !run_w : !pooled) continue;
+    cp_async_wait<0>();
+    __syncwarp();
+    if (!run_w) {  // nothing to rank here, but the staging pipeline must keep moving
+      stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
+    } else {
       uint32_t key[R];
-      uint32_t n_valid;
-      if (PHASE == 0) {
-        uint32_t nz = 0;
-        cp_async_wait<0>();
-        __syncwarp();
+      uint32_t nz = 0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const uint32_t e = r * 32 + lane;
-          uint32_t k = kKeySentinel;
-          if (e < m) {
-            // |d| bits << 1 with the sign in bit 0 is a rotate; +-0 rotate to 0 / 1
-            const uint32_t du = __float_as_uint(rawB[e] - rawA[e]), rot = __funnelshift_l(du, du, 1);
-            if (rot > 1u) {
-              k = rot;
-              ++nz;
-            }
+      for (int r = 0; r < R; ++r) {
+        const uint32_t e = r * 32 + lane;
+        uint32_t k = kKeySentinel;
+        if (e < m) {
+          // |d| bits << 1 with the sign in bit 0 is a rotate; +-0 rotate to 0 / 1
+          const uint32_t du = __float_as_uint(rawB[e] - rawA[e]), rot = __funnelshift_l(du, du, 1);
+          if (rot > 1u) {
+            k = rot;
+            ++nz;
           }
-          key[r] = k;
         }
-        n_valid = w_n = __reduce_add_sync(0xffffffffu, nz);
-        __syncwarp();  // every lane has its keys in registers: the staging buffers are free again
-        stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
-      } else {
-        const float *src = seg == 1 ? base : cur;
-        n_valid = seg == 1 ? nb : nc;
-        // unconditional loads from a clamped index: predicated ones get serialised two at a time
-        // (one predicate register each), which exposed a dozen L2 round trips per segment
-        const uint32_t last = n_valid - 1;  // pooled implies n_valid > 0
-        float x[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) x[r] = __ldg(src + min((uint32_t)(r * 32) + lane, last));
-#pragma unroll
-        for (int r = 0; r < R; ++r) key[r] = (uint32_t)(r * 32) + lane < n_valid ? float_key(x[r]) : kKeySentinel;
+        key[r] = k;
       }
+      const uint32_t n_valid = w_n = __reduce_add_sync(0xffffffffu, nz);
+      __syncwarp();  // every lane has its keys in registers: the staging buffers are free again
+      stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
       warp_bitonic_sort<R>(key, lane);
 
-      // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1)
-      const uint32_t sh = PHASE == 0 ? 1u : 0u;  // |d| keys carry the sign in bit 0
-      // slots of this lane that hold real samples (compared against literals below: a bound written
-      // as lane*R + r < n_valid gets hoisted into R loop-invariant registers, and those spilled)
+      // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1); the keys
+      // carry the sign in bit 0.  Slots of this lane that hold real samples are compared against literals
+      // below: a bound written as lane*R + r < n_valid gets hoisted into R loop-invariant registers, and
+      // those spilled
       const int rem = (int)n_valid - (int)(lane * R);
-      // fm_pidx(lane*R + r) without a shift per key: the lane's slots start at pad0 and gain one pad
-      // word at each 32-element boundary they cross (slot `cross`, and cross + 32 when R > 32)
-      const int pad0 = fm_pidx((int)(lane * R)), cross = 32 - (int)((lane * R) & 31u);
       bool tie = false;
 #pragma unroll
-      for (int r = 0; r + 1 < R; ++r) tie = tie || (((key[r] >> sh) == (key[r + 1] >> sh)) && (r + 1 < rem));
+      for (int r = 0; r + 1 < R; ++r) tie = tie || (((key[r] >> 1) == (key[r + 1] >> 1)) && (r + 1 < rem));
       const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1);
-      tie = tie || (lane < 31 && ((key[R - 1] >> sh) == (nxt >> sh)) && (R < rem));
+      tie = tie || (lane < 31 && ((key[R - 1] >> 1) == (nxt >> 1)) && (R < rem));
       const bool any_tie = __any_sync(0xffffffffu, tie);
-
-      if (PHASE == 0) {
-        long long acc = 0, tt = 0;
-        if (!any_tie) {
-          // tie-free |d|: the rank of sorted position e is e+1
-          int a32 = 0, npos = 0;
-#pragma unroll
-          for (int r = 0; r < R; ++r)
-            if (r < rem && !(key[r] & 1u)) { a32 += 2 * (r + 1); ++npos; }
-          acc = a32 + 2 * (int)(lane * R) * npos;
-        } else {
-#pragma unroll
-          for (int r = 0; r < R; ++r)
-            if (r <= rem) sB[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
-          if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
-          __syncwarp();
-          run_pass<true>(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
-          __syncwarp();
-        }
-        w_2wp = warp_sum_i64(acc);
-        w_ties = any_tie ? warp_sum_i64(tt) : 0;
-      } else {
-        uint32_t *dst = seg == 1 ? sA : sB;
+      long long acc = 0, tt = 0;
+      if (!any_tie) {
+        // tie-free |d|: the rank of sorted position e is e+1
+        int a32 = 0, npos = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r)
-          if (r <= rem) dst[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
-        if (n_valid == 32u * R && lane == 0) dst[fm_pidx(32 * R)] = kKeySentinel;
-        if (any_tie) {
-          long long tt = 0, unused = 0;
-          __syncwarp();
-          run_pass<true>(dst, R, 0u, false, lane, n_valid, seg == 1 ? rlA : rlB, &tt, &unused);
-          mw_ties += tt;  // per-lane partial of T_A + T_B, reduced below
-          if (seg == 1) tie_a = true; else tie_b = true;
-        }
+          if (r < rem && !(key[r] & 1u)) { a32 += 2 * (r + 1); ++npos; }
+        acc = a32 + 2 * (int)(lane * R) * npos;
+      } else {
+        // fm_pidx(lane*R + r) without a shift per key: the lane's slots start at pad0 and gain one pad
+        // word at each 32-element boundary they cross (slot `cross`, and cross + 32 when R > 32)
+        const int pad0 = fm_pidx((int)(lane * R)), cross = 32 - (int)((lane * R) & 31u);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (r <= rem) sB[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
+        if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
+        __syncwarp();
+        run_pass<true>(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
+        __syncwarp();
       }
+      w_2wp = warp_sum_i64(acc);
+      w_ties = any_tie ? warp_sum_i64(tt) : 0;
     }
-    if (pooled) {
-      __syncwarp();
-      int plt;
-      long long peq, x3;
-      fm_mw_walk(sA, (kTile / 33) * 32, (int)nb, (int)nc, tie_a ? rlA : nullptr, tie_b ? rlB : nullptr, (int)lane, plt, peq, x3);
-      const long long plt_sum = warp_sum_i64((long long)plt), peq_sum = warp_sum_i64(peq);
-      mw_2r1 = (long long)nb * ((long long)nb + 1) + 2 * plt_sum + peq_sum;
-      mw_ties = warp_sum_i64(mw_ties + 3 * x3);
-      __syncwarp();
-    }
-
-    // ---- exact integer statistics out; p-values and the combiner run one thread per unit in
-    //      k_rank_finalize
+    // exact integer statistics out; p-values and the combiner run one thread per unit in k_rank_finalize
     if (lane == 0 && have) {
       fm_series_score *o = scores + u;
-      if (PHASE == 0) {
-        o->status = run_w ? FM_S_WILCOXON_RUN : 0u;  // first writer (scores start zeroed)
-        o->w_n = w_n;
-        o->w_2wplus = w_2wp;
-        o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
-        o->w_ties = w_ties;
-      } else {
-        // fire-and-forget OR (the Wilcoxon launch, or the zero fill, wrote the word earlier in the stream)
-        if (run_mw || run_k) atomicOr(&o->status, (run_mw ? FM_S_MW_RUN : 0u) | (run_k ? FM_S_KRUSKAL_RUN : 0u));
-        o->mw_2u1 = pooled ? mw_2r1 - (long long)nb * ((long long)nb + 1) : 0;
-        o->mw_2r1 = pooled ? mw_2r1 : 0;
-        o->mw_ties = pooled ? mw_ties : 0;
-      }
+      o->status = run_w ? FM_S_WILCOXON_RUN : 0u;  // first writer (scores start zeroed)
+      o->w_n = w_n;
+      o->w_2wplus = w_2wp;
+      o->w_2wminus = run_w ? (long long)w_n * ((long long)w_n + 1) - w_2wp : 0;
+      o->w_ties = w_ties;
     }
   }
 }
@@ -561,7 +474,9 @@ __global__ void __launch_bounds__(W * 32, R <= 24 ? 3 : 1) k_mw(DevBatch b, cons
       }
     }
     const float *base = b.values + off + nh, *cur = base + nb;
-    const bool fits = nb <= (uint32_t)N && nc <= (uint32_t)N && nb > 0 && nc > 0;
+    // D17: segments longer than FM_RANK_MAX_SEGMENT are not ranked; the launch picks R so that all others fit
+    const bool fits = nb <= (uint32_t)N && nc <= (uint32_t)N && nb > 0 && nc > 0 && nb <= (uint32_t)FM_RANK_MAX_SEGMENT &&
+                      nc <= (uint32_t)FM_RANK_MAX_SEGMENT;
     const bool run_mw = want_mw && nb >= min_mw && nc >= min_mw && fits;
     const bool run_k = want_k && nb >= min_k && nc >= min_k && fits;
     long long r1x2 = 0, u1x2 = 0, ties = 0;
@@ -782,72 +697,73 @@ __global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevPara
   o->kw_h = kw_h;
 }
 
+constexpr uint64_t kBlocksPerSm = 64;  // many more blocks than are resident: tie-heavy units take longer, the block
+                                       // scheduler evens it out (a persistent 5-blocks-per-SM grid measured 19 % slower)
+
 template <int R>
-cudaError_t launch(const DevBatch &b, const DevParams *dp, bool want_w, bool want_pooled, uint32_t max_seg,
-                   fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon) {
-  uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    // many more blocks than are resident: tie-heavy units take longer, the block scheduler evens it
-  // out (a persistent 5-blocks-per-SM grid measured 19 % slower)
-  const uint64_t cap = (uint64_t)sm_count * 64;
-  if (blocks > cap) blocks = cap;
+cudaError_t launch_wilcoxon(const DevBatch &b, const DevParams *dp, uint32_t max_pairs, fm_series_score *scores, int sm_count,
+                            cudaStream_t st) {
+  const uint64_t blocks = std::min<uint64_t>((b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock, (uint64_t)sm_count * kBlocksPerSm);
   if (blocks == 0) return cudaSuccess;
-  const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
-  // the two sorted runs of a unit share one element space: the second starts at element K, a multiple
-  // of 32 that leaves room for the first run and its sentinel (fm_rank_merge.h)
-  const int K = (seg_cap + 1 + 31) / 32 * 32;
-  const int tile_words = K + K / 32, rl_entries = (seg_cap + 2 + 1) & ~1;
-  const int smem = kWarpsPerBlock * 2 * (tile_words * 4 + rl_entries * 2);
-  const int raw_cap = (seg_cap + 3) & ~3;
-  const int smem_w = kWarpsPerBlock * ((33 * R + 2) * 4 + 2 * raw_cap * 4);
-  cudaError_t e = cudaFuncSetAttribute(k_rank<R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w);
+  const int raw_cap = ((int)std::min<uint32_t>(max_pairs, 32u * R) + 3) & ~3;
+  const int smem = kWarpsPerBlock * ((33 * R + 2) * 4 + 2 * raw_cap * 4);
+  cudaError_t e = cudaFuncSetAttribute(k_wilcoxon<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_rank<R, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
-  if (want_w) k_rank<R, 0><<<(unsigned)blocks, kWarpsPerBlock * 32, smem_w, st>>>(b, dp, scores, tile_words, raw_cap);
-  if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
-  static const bool old_walk = getenv("FOREMAST_GPU_MW_WALK") != nullptr;  // A/B switch: sort both samples + merge-path walk
-  if (want_pooled && old_walk) k_rank<R, 1><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, tile_words, rl_entries);
-  if (want_pooled && !old_walk) {
-    constexpr int W = R >= 48 ? 4 : (R == 32 ? 6 : 8);
-    constexpr int N = 32 * R;
-    const int rl_cap = seg_cap + 2, key_words = ((seg_cap + 7) & ~7) + 8;  // a chunk may start just below seg_cap
-    // id table of the duplicate search: as many u16 slots as fit while three blocks stay resident per SM
-    // (fewer slots -> more keys need a second round), never fewer than its later tenants need (counters +
-    // run lengths) nor than 1.25 keys' worth, and no more than 4 per key
-    const int budget = (227 * 1024 - 3 * 1024) / (3 * W) / 16 * 16 - ((N + 4) + key_words) * 4;
-    int n_slots = std::max(std::max(N + rl_cap, seg_cap + seg_cap / 4), std::min(budget / 2, 4 * seg_cap));
-    n_slots = (n_slots + 7) & ~7;
-    const int smem_mw = W * ((N + 4) + key_words + n_slots / 2) * 4;
-    e = cudaFuncSetAttribute(k_mw<R, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_mw);
-    if (e != cudaSuccess) return e;
-    uint64_t mw_blocks = (b.n_units + W - 1) / W;
-    if (mw_blocks > cap) mw_blocks = cap;
-    k_mw<R, W><<<(unsigned)mw_blocks, W * 32, smem_mw, st>>>(b, dp, scores, rl_cap, key_words, n_slots);
-  }
-  k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
+  k_wilcoxon<R><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, raw_cap);
   return cudaGetLastError();
 }
 
+template <int R>
+cudaError_t launch_mw(const DevBatch &b, const DevParams *dp, uint32_t max_seg, fm_series_score *scores, int sm_count,
+                      cudaStream_t st) {
+  constexpr int W = R >= 48 ? 4 : (R == 32 ? 6 : 8);
+  constexpr int N = 32 * R;
+  const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
+  const int rl_cap = seg_cap + 2, key_words = ((seg_cap + 7) & ~7) + 8;  // a chunk may start just below seg_cap
+  // id table of the duplicate search: as many u16 slots as fit while three blocks stay resident per SM
+  // (fewer slots -> more keys need a second round), never fewer than its later tenants need (counters +
+  // run lengths) nor than 1.25 keys' worth, and no more than 4 per key
+  const int budget = (227 * 1024 - 3 * 1024) / (3 * W) / 16 * 16 - ((N + 4) + key_words) * 4;
+  int n_slots = std::max(std::max(N + rl_cap, seg_cap + seg_cap / 4), std::min(budget / 2, 4 * seg_cap));
+  n_slots = (n_slots + 7) & ~7;
+  const int smem = W * ((N + 4) + key_words + n_slots / 2) * 4;
+  cudaError_t e = cudaFuncSetAttribute(k_mw<R, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const uint64_t blocks = std::min<uint64_t>((b.n_units + W - 1) / W, (uint64_t)sm_count * kBlocksPerSm);
+  if (blocks == 0) return cudaSuccess;
+  k_mw<R, W><<<(unsigned)blocks, W * 32, smem, st>>>(b, dp, scores, rl_cap, key_words, n_slots);
+  return cudaGetLastError();
+}
+
+// the sort sizes: R keys per lane, R = 2^q or 3*2^q
+#define FM_FOR_SORT_SIZE(n, CALL)                                                                    \
+  ((n) <= 32 ? CALL(1) : (n) <= 64 ? CALL(2) : (n) <= 96 ? CALL(3) : (n) <= 128 ? CALL(4) : (n) <= 192 ? CALL(6)      \
+   : (n) <= 256 ? CALL(8) : (n) <= 384 ? CALL(12) : (n) <= 512 ? CALL(16) : (n) <= 768 ? CALL(24)   \
+   : (n) <= 1024 ? CALL(32) : (n) <= 1536 ? CALL(48) : CALL(64))
+
 }  // namespace
 
-// max_seg = longest baseline / current segment in the batch; segments above 2048 samples are
-// not ranked by this kernel (the caller reports FM_E_UNSUPPORTED).
-cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_seg,
+// max_base / max_cur = longest baseline / current segment in the batch.  Units whose segments exceed
+// FM_RANK_MAX_SEGMENT samples are not ranked (D17: Mann-Whitney / Kruskal need both segments within the
+// limit, Wilcoxon its min(n_base, n_cur) pairs); the sort size is chosen for the rest.
+cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
                            fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon) {
   const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
   const bool w = all || pairwise == FM_PW_WILCOXON;
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
-  if (max_seg <= 32) return launch<1>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 64) return launch<2>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 96) return launch<3>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 128) return launch<4>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 192) return launch<6>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 256) return launch<8>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 384) return launch<12>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 512) return launch<16>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 768) return launch<24>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 1024) return launch<32>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 1536) return launch<48>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  if (max_seg <= 2048) return launch<64>(b, dp, w, pooled, max_seg, scores, sm_count, st, after_wilcoxon);
-  return cudaErrorInvalidValue;
+  const uint32_t cap = FM_RANK_MAX_SEGMENT;
+  const uint32_t max_pairs = std::min(std::min(max_base, max_cur), cap);  // bounds min(n_base, n_cur) of every unit
+  const uint32_t max_seg = std::min(std::max(max_base, max_cur), cap);
+  cudaError_t e = cudaSuccess;
+#define FM_W(R) launch_wilcoxon<R>(b, dp, max_pairs, scores, sm_count, st)
+#define FM_M(R) launch_mw<R>(b, dp, max_seg, scores, sm_count, st)
+  if (w) e = FM_FOR_SORT_SIZE(max_pairs, FM_W);
+  if (e != cudaSuccess) return e;
+  if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
+  if (pooled) e = FM_FOR_SORT_SIZE(max_seg, FM_M);
+  if (e != cudaSuccess) return e;
+#undef FM_W
+#undef FM_M
+  if (b.n_units) k_rank_finalize<<<(unsigned)((b.n_units + 255) / 256), 256, 0, st>>>(b, dp, scores);
+  return cudaGetLastError();
 }

@@ -272,9 +272,13 @@ void fm_batch_free(fm_batch *b);
 
 /* The scoring pass itself: pairwise tests -> threshold adjust -> band models -> anomaly flags ->
  * per-service verdicts (docs/guides/design.md:35,43).  Asynchronous on the context's stream;
- * accessors synchronise.  Limits: with a pairwise test enabled, baseline and current segments may
- * hold at most 2048 samples each (FM_E_UNSUPPORTED beyond; the reference's windows are 30-1440
- * one-minute points); history length is only bounded by memory. */
+ * accessors synchronise.  Rank tests work on segments of up to FM_RANK_MAX_SEGMENT samples (the
+ * reference's baseline / current windows are 30-1440 one-minute points): a unit whose baseline or
+ * current segment is longer has Mann-Whitney and Kruskal-Wallis not run, a unit with more than that many
+ * PAIRS has Wilcoxon not run (status bits FM_S_*_RUN stay clear, p = 1, exactly like a unit with too
+ * few points, oracle/DECISIONS.md D17) and everything else of the unit and of the batch is scored as
+ * usual.  History length is only bounded by memory. */
+#define FM_RANK_MAX_SEGMENT 2048
 int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out);
 /* One-shot, host in / host out: chunked H2D overlapped with scoring, verdicts copied back.
  * `verdicts` has room for n_services entries. */

@@ -198,9 +198,11 @@ static int score_unit(const fm_params *p, const float *hist, uint32_t nh, const 
   int want_w = p->pairwise == FM_PW_ALL || p->pairwise == FM_PW_ANY || p->pairwise == FM_PW_WILCOXON;
   int want_k = p->pairwise == FM_PW_ALL || p->pairwise == FM_PW_ANY || p->pairwise == FM_PW_KRUSKAL;
   uint32_t m = nb < nc ? nb : nc;
-  int run_mw = want_mw && nb >= p->min_mann_white && nc >= p->min_mann_white && m > 0;
-  int run_w = want_w && m >= p->min_wilcoxon && m > 0;
-  int run_k = want_k && nb >= p->min_kruskal && nc >= p->min_kruskal && m > 0;
+  /* D17: rank tests look at segments of at most FM_RANK_MAX_SEGMENT samples (Wilcoxon: pairs) */
+  int short_enough = nb <= FM_RANK_MAX_SEGMENT && nc <= FM_RANK_MAX_SEGMENT;
+  int run_mw = want_mw && nb >= p->min_mann_white && nc >= p->min_mann_white && m > 0 && short_enough;
+  int run_w = want_w && m >= p->min_wilcoxon && m > 0 && m <= FM_RANK_MAX_SEGMENT;
+  int run_k = want_k && nb >= p->min_kruskal && nc >= p->min_kruskal && m > 0 && short_enough;
   int n_run = 0, n_rej = 0;
   if (run_mw || run_k) {
     uint32_t N = nb + nc;

@@ -298,12 +298,22 @@ def test_edge_cases(ctx, oracle):
     assert r.series().size == 0 and r.verdicts().size == 0
     r.free()
     e.free()
+    # ... also through the two bulk host paths, with no arrays at all (n_units = 0, NULL pointers)
+    import ctypes as C
+    L, h = ctx._L, C.c_void_p()
+    empty = abi.Csr(0, None, None, None, None, None)
+    assert L.fm_batch_from_csr(ctx._h, C.byref(empty), C.byref(h)) == 0
+    L.fm_batch_free(h)
+    assert L.fm_score_host(ctx._h, C.byref(empty), C.byref(p), 0, None) in (0, abi.E_INVALID)
+    one = np.zeros(1, dtype=abi.VERDICT)
+    assert L.fm_score_host(ctx._h, C.byref(empty), C.byref(p), 1, one.ctypes.data) == 0
+    assert int(one[0]["n_units"]) == 0 and int(one[0]["verdict"]) == abi.V_UNKNOWN
 
 
 def test_size_limits(ctx, oracle):
     """Longest inputs: a 50 000-sample history streams through the band kernel; rank segments above
-    2048 samples are refused with FM_E_UNSUPPORTED (and scored fine once the rank tests are off)."""
-    from foremast_b200._lib import ForemastGpuError
+    FM_RANK_MAX_SEGMENT (2048) samples make that ONE unit's rank tests "not run" (D17) while the rest of the
+    unit and of the batch is scored as usual -- e.g. a 7-day baseline against a 30-minute current window."""
     rng = np.random.default_rng(2)
     z = rng.normal(50, 3, 60000).astype(np.float32)
     b = ctx.batch_from_units([(z[:50000], z[50000:52048], z[52048:54096]), (z[:37], z[100:140], z[200:260])],
@@ -311,12 +321,23 @@ def test_size_limits(ctx, oracle):
     p = full_params(oracle)
     check_batch(ctx, oracle, b, p)
     b.free()
-    big = ctx.batch_from_units([(z[:100], z[100:2200], z[3000:3100])])
-    with pytest.raises(ForemastGpuError) as ei:
-        ctx.score(big, p)
-    assert ei.value.code == abi.E_UNSUPPORTED
-    p.pairwise = abi.PW_NONE
-    check_batch(ctx, oracle, big, p)
+    units = [(z[:100], z[100:2200], z[3000:3100]),          # baseline 2100 > 2048: MWU / KW off, Wilcoxon on 100 pairs
+             (z[:0], z[5000:15080], z[20000:20030]),        # 7-day baseline vs 30 points, baseline is the model window
+             (z[:64], z[1000:4000], z[6000:9000]),          # 3000 pairs: nothing ranked
+             (z[:64], z[100:140], z[200:260]),              # an ordinary unit beside them
+             (z[:64], z[300:2348], z[2400:4448])]           # exactly 2048 / 2048: everything runs
+    big = ctx.batch_from_units(units, service_id=[0, 0, 1, 1, 2], metric_type=[abi.MT_CPU] * 5)
+    for pairwise in (abi.PW_ALL, abi.PW_ANY, abi.PW_WILCOXON, abi.PW_MANN_WHITE, abi.PW_NONE):
+        p.pairwise = pairwise
+        got, _ = check_batch(ctx, oracle, big, p)
+    p.pairwise = abi.PW_ALL
+    got, _ = check_batch(ctx, oracle, big, p)
+    run = lambda u, bit: bool(int(got["status"][u]) & bit)  # noqa: E731
+    assert not run(0, abi.S_MW_RUN) and not run(0, abi.S_KRUSKAL_RUN) and run(0, abi.S_WILCOXON_RUN)
+    assert not run(1, abi.S_MW_RUN) and run(1, abi.S_WILCOXON_RUN)
+    assert not (run(2, abi.S_MW_RUN) or run(2, abi.S_KRUSKAL_RUN) or run(2, abi.S_WILCOXON_RUN))
+    assert run(3, abi.S_MW_RUN) and run(3, abi.S_WILCOXON_RUN) and run(3, abi.S_KRUSKAL_RUN)
+    assert run(4, abi.S_MW_RUN) and run(4, abi.S_WILCOXON_RUN) and run(4, abi.S_KRUSKAL_RUN)
     big.free()
 
 
