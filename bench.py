@@ -300,7 +300,46 @@ def run_ours(args):
         for _ in range(200):
             ctx.score_host(h0, q, 1)
         other["cfg0_single_canary_job_5_series"] = {"us_per_call": (time.perf_counter() - t0) / 200 * 1e6,
-                                                    "note": "fm_score_host, launch-latency bound; 5 launches + pool allocations + one D2H"}
+                                                    "note": "fm_score_host small-job path: one upload, one clear, the launches, one download; no allocation"}
+        # ingest: Prometheus query_range response bodies -> sealed batch -> verdicts, cfg2's shape
+        # (80 k series x 1440 points: 10 000 aliases with one 1380-point history series and eight 60-point current
+        # series each), through fm_batch_add_prometheus_many on all host threads.  The same two bodies are lent
+        # to every job (the scanner reads them 10 000 times; generating 450 MB of distinct text would take longer
+        # than everything else in this bench).
+        def prom_body(n_series, n_points, seed):
+            r = np.random.default_rng(seed)
+            return json.dumps({"status": "success", "data": {"resultType": "matrix", "result": [
+                {"metric": {"__name__": "namespace_app_pod_cpu_usage_seconds_total", "pod": f"pod-{i}", "namespace": "dev"},
+                 "values": [[1550000000 + 60 * k, f"{v:.4f}"] for k, v in enumerate(r.normal(0.45, 0.08, n_points))]}
+                for i in range(n_series)]}}).encode()
+        hb, cb = prom_body(1, 1380, 1), prom_body(8, 60, 2)
+        n_jobs = 10_000
+        jobs = [(j // 10, abi.MT_CPU, 60.0, hb, None, cb) for j in range(n_jobs)]
+        json_mb = n_jobs * (len(hb) + len(cb)) / 1e6
+        q = bench_params(default_params()); q.algorithms = abi.ALG_EWMA | abi.ALG_DES; q.pairwise = abi.PW_NONE
+        ts_pack, ts_total = [], []
+        for i in range(3):
+            t0 = time.perf_counter()
+            bb, per = ctx.batch_from_prometheus(jobs, threads=0)
+            t1 = time.perf_counter()
+            res = ctx.score(bb, q)
+            res.verdicts()
+            t2 = time.perf_counter()
+            res.free()
+            bb.free()
+            if i:
+                ts_pack.append(t1 - t0)
+                ts_total.append(t2 - t0)
+        t0 = time.perf_counter()
+        bb, _ = ctx.batch_from_prometheus(jobs[:n_jobs // 16], threads=1)
+        one_thread_s = time.perf_counter() - t0
+        bb.free()
+        other["ingest_prometheus_json_cfg2_shape"] = {
+            "json_mb": json_mb, "units": int(per.sum()), "host_threads": host_threads(),
+            "parse_pack_upload_ms": min(ts_pack) * 1e3, "json_mb_per_s_all_threads": json_mb / min(ts_pack),
+            "json_mb_per_s_one_thread": json_mb / 16 / one_thread_s,
+            "json_in_to_verdicts_out_ms": min(ts_total) * 1e3,
+            "note": "fm_batch_add_prometheus_many (timestamps read, missing scrapes re-gridded) + fm_batch_seal + EWMA/DES scoring + verdicts"}
 
     # ---- end to end through the public one-shot call: pinned host CSR -> H2D -> score -> verdicts D2H
     host = batch.download()

@@ -114,6 +114,16 @@ PROM_SERIES = np.dtype([("metric_off", "<u8"), ("metric_len", "<u8"), ("t0", "<f
 assert PROM_SERIES.itemsize == 48
 
 
+PROM_GRID, PROM_FILL = 1, 2
+
+
+class PromJob(C.Structure):
+    """fm_prom_job: the three query_range response bodies of one job alias."""
+    _fields_ = [("meta", SeriesMeta), ("reserved", C.c_uint32), ("step", C.c_double),
+                ("hist_json", C.c_char_p), ("base_json", C.c_char_p), ("cur_json", C.c_char_p),
+                ("hist_len", C.c_uint64), ("base_len", C.c_uint64), ("cur_len", C.c_uint64)]
+
+
 class HostCsr:
     """A host-side ragged CSR batch (numpy arrays) in the layout of `fm_csr`."""
 

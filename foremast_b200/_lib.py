@@ -28,6 +28,10 @@ SYMBOLS = {
     "fm_host_free": (None, [_P, _P]),
     "fm_parse_prometheus_matrix": (C.c_int, [C.c_char_p, C.c_uint64, _P, C.c_uint32, C.POINTER(C.c_uint32), _P,
                                               C.c_uint64, C.POINTER(C.c_uint64)]),
+    "fm_parse_prometheus_matrix_grid": (C.c_int, [C.c_char_p, C.c_uint64, C.c_uint32, C.c_double, _P, C.c_uint32,
+                                                   C.POINTER(C.c_uint32), _P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "fm_batch_add_prometheus": (C.c_int, [_P, C.POINTER(abi.PromJob), C.c_uint32, C.POINTER(C.c_uint32)]),
+    "fm_batch_add_prometheus_many": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, _P]),
     "fm_batch_begin": (C.c_int, [_P, C.c_uint64, C.c_uint64, _PP]),
     "fm_batch_add_series": (C.c_int, [_P, C.POINTER(abi.SeriesMeta), _P, C.c_uint32, _P, C.c_uint32, _P, C.c_uint32]),
     "fm_batch_seal": (C.c_int, [_P]),

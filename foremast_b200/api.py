@@ -140,6 +140,28 @@ class Context:
         self._check(self._L.fm_batch_seal(h))
         return b
 
+    def batch_from_prometheus(self, jobs, flags=abi.PROM_GRID | abi.PROM_FILL, threads=0):
+        """Response bodies -> sealed batch without Python in the loop (fm_batch_add_prometheus_many).
+        jobs = [(service_id, metric_type, step_seconds, hist_body, base_body, cur_body), ...] (bodies are
+        bytes or None).  Returns (batch, units_per_job); a job whose bodies do not parse gets -1 units."""
+        n = len(jobs)
+        arr = (abi.PromJob * max(n, 1))()
+        keep = []
+        for i, (sid, mt, step, hb, bb, cb) in enumerate(jobs):
+            j = arr[i]
+            j.meta.service_id, j.meta.metric_type, j.step = int(sid), int(mt), float(step)
+            for name, body in (("hist", hb), ("base", bb), ("cur", cb)):
+                keep.append(body)
+                setattr(j, name + "_json", body)
+                setattr(j, name + "_len", len(body) if body else 0)
+        h = C.c_void_p()
+        self._check(self._L.fm_batch_begin(self._h, n, 0, C.byref(h)))
+        b = Batch(self, h)
+        per = np.zeros(max(n, 1), np.uint32)
+        self._check(self._L.fm_batch_add_prometheus_many(h, arr, n, flags, threads, per.ctypes.data))
+        self._check(self._L.fm_batch_seal(h))
+        return b, np.where(per[:n] == 0xFFFFFFFF, -1, per[:n].astype(np.int64))
+
     def batch_from_csr(self, csr):
         h = C.c_void_p()
         st = csr.as_struct()

@@ -63,24 +63,35 @@ def query_window(url):
     return num("start", 0.0), num("end", 0.0), num("step", float(STEP_SECONDS))
 
 
-def parse_matrix_native(body):
-    """Response body (bytes) -> [(labels, t0, float32 values)] through the library's one-pass
-    scanner (fm_parse_prometheus_matrix): no DOM, samples parsed straight into one float array."""
+def parse_matrix_series(body, flags=0, step_hint=0.0):
+    """Response body (bytes) -> (fm_prom_series records, float32 values) through the library's scanner.
+    flags = abi.PROM_GRID [| abi.PROM_FILL] places the samples on the query grid (missing scrapes become
+    NaN, or the previous sample), so that sample index and time stay aligned; `reserved` of a record tells
+    how many grid slots the series lacks."""
     import ctypes as C
     from ._lib import ForemastGpuError, load
     L = load()
     if isinstance(body, str):
         body = body.encode()
     ns, nv = C.c_uint32(), C.c_uint64()
-    rc = L.fm_parse_prometheus_matrix(body, len(body), None, 0, C.byref(ns), None, 0, C.byref(nv))
+    rc = L.fm_parse_prometheus_matrix_grid(body, len(body), flags, step_hint, None, 0, C.byref(ns), None, 0, C.byref(nv))
     if rc not in (abi.OK, abi.E_RANGE):
         raise ForemastGpuError(rc, "malformed Prometheus response")
     series = np.zeros(ns.value, dtype=abi.PROM_SERIES)
     values = np.empty(nv.value, np.float32)
-    rc = L.fm_parse_prometheus_matrix(body, len(body), series.ctypes.data, ns.value, C.byref(ns),
-                                      values.ctypes.data, nv.value, C.byref(nv))
+    rc = L.fm_parse_prometheus_matrix_grid(body, len(body), flags, step_hint, series.ctypes.data, ns.value, C.byref(ns),
+                                           values.ctypes.data, nv.value, C.byref(nv))
     if rc:
         raise ForemastGpuError(rc, "malformed Prometheus response")
+    return series, values
+
+
+def parse_matrix_native(body, flags=0, step_hint=0.0):
+    """Response body (bytes) -> [(labels, t0, float32 values)] through the library's one-pass
+    scanner (fm_parse_prometheus_matrix): no DOM, samples parsed straight into one float array."""
+    if isinstance(body, str):
+        body = body.encode()
+    series, values = parse_matrix_series(body, flags, step_hint)
     out = []
     for s in series:
         labels = json.loads(body[int(s["metric_off"]):int(s["metric_off"] + s["metric_len"])]) if s["metric_len"] else {}
@@ -203,63 +214,232 @@ def reason_text(anomalies):
     return html.escape(json.dumps({"anomaly": body}), quote=True)
 
 
+# status vocabulary of the job document, foremast-service/pkg/converter/converter.go:12-25
+ST_INITIAL, ST_PRE_INPROGRESS, ST_PRE_COMPLETED, ST_PRE_FAILED = "initial", "preprocess_inprogress", "preprocess_completed", "preprocess_failed"
+ST_POST_INPROGRESS = "postprocess_inprogress"
+MAX_STUCK_IN_SECONDS = 90  # deploy/foremast/3_brain/foremast-brain.yaml:80-81
+HPA_METRIC = "namespace_app_per_pod:hpa_score"  # examples/hpa/README.MD:59 (foremastbrain:namespace_app_per_pod:hpa_score)
+
+
+class DictStore:
+    """Dict-backed stand-in of the job store the brain polls and writes back to: the `documents` index
+    (ByStatus, "used by backend python model", foremast-service/pkg/search/elasticsearchstore.go:154-180)
+    and the `hpalogs` index (GetLogs, :203-228).  The worker only needs these three calls; an
+    Elasticsearch-backed store has the same shape."""
+
+    def __init__(self, docs=()):
+        self.docs = {d["id"]: dict(d) for d in docs}
+        self.hpalogs = []
+
+    def by_status(self, statuses, limit=None):
+        out = [dict(d) for d in self.docs.values() if d.get("status", ST_INITIAL) in statuses]
+        return out[:limit] if limit else out
+
+    def update(self, doc_id, fields):
+        self.docs[doc_id].update(fields)
+
+    def add_hpalog(self, log):
+        self.hpalogs.append(log)
+
+
+def hpa_score(details, sla_metric="latency", load_metric="tps"):
+    """The 0-100 score the HPA object targets at 50 (examples/hpa/README.MD:25-75), from the rule of
+    docs/dynamic_autoscaling.md:31-55.  details = [{"metricType", "current", "upper", "lower"}, ...]
+    (models.go:198-205).  Trend of the load metric: above its band = UP, below = DOWN, inside = none.
+    Reward R(action): while the SLA metric stays inside its band, scaling DOWN is rewarded and UP is not;
+    once it leaves the band, the other way round.  Score > 50 only for a rewarded UP, < 50 only for a
+    rewarded DOWN, by how far the load left its band (in band widths, capped at one) [decision D18]."""
+    by = {}
+    for d in details:
+        by.setdefault(d["metricType"], d)
+    load, sla = by.get(load_metric), by.get(sla_metric)
+    if load is None:
+        return 50, "no load metric"
+    meets_sla = sla is None or sla["current"] <= sla["upper"]
+    width = max(load["upper"] - load["lower"], 1e-12)
+    if load["current"] > load["upper"] and not meets_sla:
+        s = min(1.0, (load["current"] - load["upper"]) / width)
+        return int(round(50 + 50 * s)), f"{load_metric} above its band and {sla_metric} above its band: scale up"
+    if load["current"] < load["lower"] and meets_sla:
+        s = min(1.0, (load["lower"] - load["current"]) / width)
+        return int(round(50 - 50 * s)), f"{load_metric} below its band and {sla_metric} within its band: scale down"
+    return 50, "no rewarded scaling action"
+
+
 class BrainWorker:
-    """process(document) -> the fields the brain writes back into the job document."""
+    """The brain's loop at the Elasticsearch seam, batched: many job documents -> ONE batch -> one scoring
+    pass (service_id = job index), then per job the fields the brain writes back.
 
-    def __init__(self, ctx, fetch, params, step=STEP_SECONDS, clock=time.time):
+    process_many(docs) is the batch form; process(doc) the single-job form (same code, one job);
+    run_once(store) claims open jobs from a store (status transitions initial -> preprocess_inprogress ->
+    preprocess_completed -> postprocess_inprogress | completed_*, converter.go:12-25, stuck jobs taken over
+    after MAX_STUCK_IN_SECONDS) and writes the results back.  `fetch(url)` returns a response body (bytes /
+    str) or an already decoded dict.  Response bodies go into the batch through the library's scanner
+    (fm_batch_add_prometheus_many): no Python per sample."""
+
+    def __init__(self, ctx, fetch, params, step=STEP_SECONDS, clock=time.time, max_stuck_seconds=MAX_STUCK_IN_SECONDS,
+                 gap_flags=abi.PROM_GRID | abi.PROM_FILL, parse_threads=0):
         self.ctx, self.fetch, self.params, self.step, self.clock = ctx, fetch, params, step, clock
+        self.max_stuck_seconds, self.gap_flags, self.parse_threads = max_stuck_seconds, gap_flags, parse_threads
 
-    def _fetch_all(self, config, start, end):
+    # ---- fetch
+    def _bodies(self, config, start, end):
+        """{alias: (body bytes, step seconds)} of one config string."""
         out = {}
         for alias, url in parse_config(config).items():
-            out[alias] = parse_matrix(self.fetch(substitute_times(url, start, end)))
+            u = substitute_times(url, start, end)
+            body = self.fetch(u)
+            if isinstance(body, dict):
+                body = json.dumps(body)
+            if isinstance(body, str):
+                body = body.encode()
+            out[alias] = (body, query_window(u)[2])
         return out
 
-    def process(self, doc):
+    # ---- the batched pass
+    def process_many(self, docs, store=None):
         now = self.clock()
-        start = doc.get("startTimeUnix", now - 30 * 60)
-        end = doc.get("endTimeUnix", now)
-        try:
-            cur = self._fetch_all(doc.get("currentConfig", ""), start, min(end, now))
-            base = self._fetch_all(doc.get("baselineConfig", ""), start, end)
-            hist = self._fetch_all(doc.get("historicalConfig", ""), now - 7 * 86400, now)
-        except Exception as e:  # bad config / store error: converter.go:22-23
-            return {"status": "preprocess_failed", "statusCode": "500", "reason": f"metric fetch failed: {e}"}
-        units, meta = build_units(hist, base, cur)
-        if not units:
-            return {"status": "completed_unknown", "statusCode": "200", "reason": "no current metric"}
-        batch = self.ctx.batch_from_units(units, service_id=[0] * len(units),
-                                          metric_type=[m["metric_type"] for m in meta])
-        res = self.ctx.score(batch, self.params)
-        verdict = res.verdicts()[0]
-        scores = res.series()
-        anomalies = []
-        if int(verdict["verdict"]) == abi.V_UNHEALTH:
-            for a in range(abi.N_ALG):
-                if not self.params.algorithms & (1 << a):
-                    continue
-                offsets, idx, val = res.anomalies(1 << a)
-                for u in np.flatnonzero(np.diff(offsets.astype(np.int64))):
-                    sl = slice(int(offsets[u]), int(offsets[u + 1]))
-                    m = meta[u]
-                    anomalies.append({"alias": m["alias"], "tags": json.dumps(m["labels"], sort_keys=True),
-                                      "algorithm": abi.ALG_NAMES[1 << a],
-                                      "pairs": anomaly_pairs(m["t0"], self.step, idx[sl], val[sl])})
-                if anomalies:
-                    break  # the first enabled algorithm that flagged something names the reason
-        res.free()
-        batch.free()
-        status = abi.V_STATUS[int(verdict["verdict"])]
-        if status == "completed_health" and now < end:
-            status = "postprocess_inprogress"  # keep watching until endTime (docs/guides/design.md:43)
-        out = {"status": status, "statusCode": "200", "modified_at": now,
-               "processingContent": json.dumps({"units": len(units), "differs": int(((scores["status"] & abi.S_DIFFERS) != 0).sum())})}
-        if anomalies:
-            out["reason"] = reason_text(anomalies)
-            info = {}
-            for a in anomalies:  # one entry per metric (models.go:78-81): the first anomalous series of the alias
-                info.setdefault(a["alias"], {"tags": a["tags"], "values": a["pairs"]})
-            out["anomalyInfo"] = json.dumps(info)
-        elif status == "completed_unknown":
-            out["reason"] = "current metric is not available"
-        return out
+        results = [None] * len(docs)
+        jobs, owners = [], []  # one fm_prom_job per (document, alias); owners[k] = (doc index, alias, current body)
+        ends = []
+        for di, doc in enumerate(docs):
+            start = doc.get("startTimeUnix", now - 30 * 60)
+            end = doc.get("endTimeUnix", now)
+            ends.append(end)
+            try:
+                cur = self._bodies(doc.get("currentConfig", ""), start, min(end, now))
+                base = self._bodies(doc.get("baselineConfig", ""), start, end)
+                hist = self._bodies(doc.get("historicalConfig", ""), now - 7 * 86400, now)
+            except Exception as e:  # bad config / store error: converter.go:22-23
+                results[di] = {"status": ST_PRE_FAILED, "statusCode": "500", "reason": f"metric fetch failed: {e}"}
+                continue
+            for alias in sorted(cur):
+                cb, step = cur[alias]
+                jobs.append((di, metric_type_of(alias), step or self.step, hist.get(alias, (None, 0))[0],
+                             base.get(alias, (None, 0))[0], cb))
+                owners.append((di, alias, cb, step or self.step))
+            if store is not None:
+                store.update(doc["id"], {"status": ST_PRE_COMPLETED, "modified_at": now})
+        per_job = np.zeros(0, np.int64)
+        batch = None
+        if jobs:
+            batch, per_job = self.ctx.batch_from_prometheus(jobs, self.gap_flags, self.parse_threads)
+        n_units = int(np.clip(per_job, 0, None).sum())
+        first = np.concatenate([[0], np.cumsum(np.clip(per_job, 0, None))]).astype(np.int64)
+        for k, n in enumerate(per_job):  # a response that does not parse fails its document, not the batch
+            if n < 0 and results[owners[k][0]] is None:
+                results[owners[k][0]] = {"status": ST_PRE_FAILED, "statusCode": "500",
+                                         "reason": f"malformed Prometheus response for {owners[k][1]}"}
+        verdicts = scores = None
+        anomalies = {}
+        if n_units:
+            batch.set_shard(0, len(docs))
+            res = self.ctx.score(batch, self.params)
+            verdicts, scores = res.verdicts(), res.series()
+            if (verdicts["verdict"] == abi.V_UNHEALTH).any():
+                for a in range(abi.N_ALG):
+                    if self.params.algorithms & (1 << a):
+                        anomalies[1 << a] = res.anomalies(1 << a)  # (offsets, idx, val) of the whole batch
+            res.free()
+        if batch is not None:
+            batch.free()
+        unit_owner = np.repeat(np.arange(len(owners)), np.clip(per_job, 0, None)) if len(owners) else np.zeros(0, np.int64)
+        for di, doc in enumerate(docs):
+            if results[di] is not None:
+                continue
+            mine = [k for k, o in enumerate(owners) if o[0] == di and per_job[k] > 0]
+            if not mine:
+                results[di] = {"status": "completed_unknown", "statusCode": "200", "reason": "no current metric"}
+                continue
+            v = verdicts[di]
+            units = np.flatnonzero(np.isin(unit_owner, mine))
+            found = []
+            if int(v["verdict"]) == abi.V_UNHEALTH:
+                for alg, (offsets, idx, val) in anomalies.items():
+                    cnt = np.diff(offsets.astype(np.int64))
+                    for u in units[cnt[units] > 0]:
+                        k = int(unit_owner[u])
+                        _, alias, cb, step = owners[k]
+                        series, _ = parse_matrix_series(cb, self.gap_flags, step)  # labels and t0 of the flagged series only
+                        srec = series[int(u - first[k])]
+                        labels = json.loads(cb[int(srec["metric_off"]):int(srec["metric_off"] + srec["metric_len"])]) if srec["metric_len"] else {}
+                        sl = slice(int(offsets[u]), int(offsets[u + 1]))
+                        found.append({"alias": alias, "tags": json.dumps(labels, sort_keys=True), "algorithm": abi.ALG_NAMES[alg],
+                                      "pairs": anomaly_pairs(float(srec["t0"]), step, idx[sl], val[sl])})
+                    if found:
+                        break  # the first enabled algorithm that flagged something names the reason
+            status = abi.V_STATUS[int(v["verdict"])]
+            if status == "completed_health" and now < ends[di]:
+                status = ST_POST_INPROGRESS  # keep watching until endTime (docs/guides/design.md:43)
+            out = {"status": status, "statusCode": "200", "modified_at": now,
+                   "processingContent": json.dumps({"units": int(units.size),
+                                                    "differs": int(((scores["status"][units] & abi.S_DIFFERS) != 0).sum())})}
+            if found:
+                out["reason"] = reason_text(found)
+                info = {}
+                for a in found:  # one entry per metric (models.go:78-81): the first anomalous series of the alias
+                    info.setdefault(a["alias"], {"tags": a["tags"], "values": a["pairs"]})
+                out["anomalyInfo"] = json.dumps(info)
+            elif status == "completed_unknown":
+                out["reason"] = "current metric is not available"
+            if doc.get("strategy") == "hpa":
+                out["hpalog"] = self._hpalog(doc, mine, owners, first, scores, now)
+            results[di] = out
+        if store is not None:
+            for doc, out in zip(docs, results):
+                fields = {k: v for k, v in out.items() if k != "hpalog"}
+                store.update(doc["id"], fields)
+                if "hpalog" in out:
+                    store.add_hpalog(out["hpalog"])
+        return results
+
+    def _hpalog(self, doc, mine, owners, first, scores, now):
+        """hpalogs document of an `hpa` job (models.go:193-208): per metric the latest sample of the first
+        current series against its moving-average band (ML_ALGORITHM=moving_average_all, the documented
+        default), and the score they give."""
+        details = []
+        for k in mine:
+            _, alias, cb, step = owners[k]
+            sc = scores[int(first[k])]
+            series, values = parse_matrix_series(cb, self.gap_flags, step)
+            n0 = int(series[0]["n_values"])
+            vals = values[int(series[0]["first_value"]):int(series[0]["first_value"]) + n0]
+            vals = vals[np.isfinite(vals)]
+            if not vals.size or not int(sc["status"]) & (1 << abi.S_ALG_SHIFT):
+                continue
+            rule = self.params.rules[metric_type_of(alias)] if self.params.rules[metric_type_of(alias)].bound else self.params.rules[0]
+            up = float(sc["ma_mean"]) + float(sc["k_eff"]) * float(sc["ma_std"])
+            lo = max(float(rule.min_lower_bound), float(sc["ma_mean"]) - float(sc["k_eff"]) * float(sc["ma_std"]))
+            details.append({"metricType": alias, "current": float(vals[-1]), "upper": up, "lower": lo})
+        load = next((d["metricType"] for d in details if any(t in d["metricType"].lower() for t in ("tps", "count", "traffic"))), "tps")
+        sla = next((d["metricType"] for d in details if "latency" in d["metricType"].lower()), "latency")
+        score, why = hpa_score(details, sla_metric=sla, load_metric=load)
+        return {"job_id": doc.get("id", ""), "timestamp": float(now),
+                "hpalog": {"hpascore": score, "reason": why, "details": details}}
+
+    def process(self, doc):
+        return self.process_many([doc])[0]
+
+    # ---- the poll loop at the store
+    def claim(self, store, limit=None):
+        """Jobs to work on now: new ones, ones still being watched (postprocess_inprogress), and ones another
+        worker reserved but left untouched for max_stuck_seconds (docs/guides/design.md:39); each is
+        reserved by writing preprocess_inprogress + modified_at."""
+        now = self.clock()
+        docs = []
+        for d in store.by_status({ST_INITIAL, ST_POST_INPROGRESS, ST_PRE_INPROGRESS, ST_PRE_COMPLETED}):
+            stuck = d.get("status") in (ST_PRE_INPROGRESS, ST_PRE_COMPLETED)
+            if stuck and now - float(d.get("modified_at", 0)) <= self.max_stuck_seconds:
+                continue  # somebody else is on it
+            docs.append(d)
+            if limit and len(docs) >= limit:
+                break
+        for d in docs:
+            store.update(d["id"], {"status": ST_PRE_INPROGRESS, "modified_at": now})
+        return docs
+
+    def run_once(self, store, limit=None):
+        docs = self.claim(store, limit)
+        if docs:
+            self.process_many(docs, store)
+        return len(docs)

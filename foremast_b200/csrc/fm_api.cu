@@ -27,7 +27,31 @@ struct fm_ctx {
   std::mutex err_mu;     // last_error only: set_err may run with or without `mu` held
   std::string last_error;
   fm_comm_state comm;    // multi-GPU merge (fm_comm.cu)
+  // small-job arena of fm_score_host: one device slab + one pinned slab, made on the first small call, so that a
+  // canary job (a handful of series) costs one H2D, one clear, the launches and one D2H -- no allocation, no events
+  unsigned char *arena_dev = nullptr, *arena_host = nullptr;
+  DevParams arena_params;       // what the slab's DevParams currently holds
+  bool arena_params_valid = false;
 };
+
+namespace {
+constexpr uint64_t kArenaUnits = 1024, kArenaValues = 256 * 1024, kArenaServices = 1024;
+constexpr uint64_t a16(uint64_t x) { return (x + 255) & ~255ull; }
+// device slab layout (byte offsets); the host slab mirrors [values .. mt] for the single upload, then the verdicts
+constexpr uint64_t kOffParams = 0;
+constexpr uint64_t kOffValues = a16(sizeof(DevParams));
+constexpr uint64_t kOffOffsets = kOffValues + a16((kArenaValues + 32) * 4);
+constexpr uint64_t kOffSeg = kOffOffsets + a16((kArenaUnits + 1) * 8);
+constexpr uint64_t kOffSid = kOffSeg + a16(3 * kArenaUnits * 4);
+constexpr uint64_t kOffMt = kOffSid + a16(kArenaUnits * 4);
+constexpr uint64_t kOffScores = kOffMt + a16(kArenaUnits);  // scores | counts | worst are cleared together
+constexpr uint64_t kOffCounts = kOffScores + a16((kArenaUnits + 1) * sizeof(fm_series_score));
+constexpr uint64_t kOffWorst = kOffCounts + a16((4 * kArenaServices + 4) * 4);
+constexpr uint64_t kOffUstat = kOffWorst + a16((kArenaServices + 1) * 8);
+constexpr uint64_t kOffUpts = kOffUstat + a16((kArenaUnits + 1) * 4);
+constexpr uint64_t kOffVerdicts = kOffUpts + a16((kArenaUnits + 1) * 4);
+constexpr uint64_t kArenaBytes = kOffVerdicts + a16((kArenaServices + 1) * sizeof(fm_verdict));
+}  // namespace
 
 struct fm_batch {
   fm_ctx *ctx = nullptr;
@@ -340,6 +364,8 @@ void fm_shutdown(fm_ctx *ctx) {
   fm_comm_destroy(ctx);
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->arena_dev) cudaFree(ctx->arena_dev);
+  if (ctx->arena_host) cudaFreeHost(ctx->arena_host);
   for (auto &e : ctx->timer)
     if (e) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
@@ -1026,6 +1052,71 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
   }
   const uint64_t n = h->n_units, n_vals = (uint64_t)h->offsets[n];
   cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
+  if (n <= kArenaUnits && n_vals <= kArenaValues && n_services <= kArenaServices && !p->band_algorithm) {
+    // ---- small job (the reference's own shape: one deployment, a handful of series, 10-30 minute windows,
+    //      foremast-barrelman/pkg/controller/DeploymentController.go:48): latency, not throughput
+    if (!ctx->arena_dev) {
+      FM_CUDA(ctx, cudaMalloc(&ctx->arena_dev, kArenaBytes));
+      FM_CUDA(ctx, cudaMallocHost(&ctx->arena_host, kArenaBytes));
+    }
+    unsigned char *dv = ctx->arena_dev, *hs = ctx->arena_host;
+    DevParams hp;
+    resolve_params(p, &hp);
+    uint64_t up0 = kOffValues;
+    if (!ctx->arena_params_valid || memcmp(&hp, &ctx->arena_params, sizeof(hp)) != 0) {
+      memcpy(hs + kOffParams, &hp, sizeof(hp));  // new parameters ride along with the samples
+      ctx->arena_params = hp;
+      ctx->arena_params_valid = true;
+      up0 = kOffParams;
+    }
+    memcpy(hs + kOffValues, h->values, n_vals * 4);
+    memset(hs + kOffValues + n_vals * 4, 0, 32 * 4);
+    memcpy(hs + kOffOffsets, h->offsets, (n + 1) * 8);
+    memcpy(hs + kOffSeg, h->seg_lens, 3 * n * 4);
+    if (h->service_id) memcpy(hs + kOffSid, h->service_id, n * 4); else memset(hs + kOffSid, 0, n * 4);
+    if (h->metric_type) memcpy(hs + kOffMt, h->metric_type, n); else memset(hs + kOffMt, 0, n);
+    // one upload: everything between the first byte that changed and the end of the per-unit arrays (the slab
+    // is laid out in upload order; the unused tail of the value area travels too when the batch is tiny, so
+    // the value area is copied separately once it is mostly empty)
+    if (n_vals * 4 + 128 < (kArenaValues * 4) / 8) {
+      FM_CUDA(ctx, cudaMemcpyAsync(dv + up0, hs + up0, kOffValues - up0 + (n_vals + 32) * 4, cudaMemcpyHostToDevice, st));
+      FM_CUDA(ctx, cudaMemcpyAsync(dv + kOffOffsets, hs + kOffOffsets, kOffScores - kOffOffsets, cudaMemcpyHostToDevice, st));
+    } else {
+      FM_CUDA(ctx, cudaMemcpyAsync(dv + up0, hs + up0, kOffScores - up0, cudaMemcpyHostToDevice, st));
+    }
+    FM_CUDA(ctx, cudaMemsetAsync(dv + kOffScores, 0, kOffUstat - kOffScores, st));
+    tb.d_values = reinterpret_cast<float *>(dv + kOffValues);
+    tb.d_offsets = reinterpret_cast<int64_t *>(dv + kOffOffsets);
+    tb.d_seg = reinterpret_cast<uint32_t *>(dv + kOffSeg);
+    tb.d_sid = reinterpret_cast<uint32_t *>(dv + kOffSid);
+    tb.d_mt = dv + kOffMt;
+    tb.n_units = n;
+    tb.n_values = n_vals + 32;
+    tb.sealed = true;
+    fm_result sr;  // lives on this frame: nothing in it is owned
+    sr.ctx = ctx;
+    sr.batch = &tb;
+    sr.n_units = n;
+    sr.n_services = n_services;
+    sr.params = *p;
+    sr.d_params = reinterpret_cast<DevParams *>(dv + kOffParams);
+    sr.d_scores = reinterpret_cast<fm_series_score *>(dv + kOffScores);
+    sr.d_counts = reinterpret_cast<uint32_t *>(dv + kOffCounts);
+    sr.d_worst = reinterpret_cast<unsigned long long *>(dv + kOffWorst);
+    sr.d_unit_status = reinterpret_cast<uint32_t *>(dv + kOffUstat);
+    sr.d_unit_points = reinterpret_cast<uint32_t *>(dv + kOffUpts);
+    sr.d_verdicts = reinterpret_cast<fm_verdict *>(dv + kOffVerdicts);
+    rc = launch_range(ctx, &sr, &tb, p, 0, n, false);
+    if (rc) { cudaStreamSynchronize(st); return rc; }
+    if (n_services) {
+      fm_launch_verdict_finalize(n_services, sr.d_counts, sr.d_worst, sr.d_verdicts, st);
+      FM_CUDA(ctx, cudaGetLastError());
+      FM_CUDA(ctx, cudaMemcpyAsync(hs + kOffVerdicts, sr.d_verdicts, n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, st));
+    }
+    FM_CUDA(ctx, cudaStreamSynchronize(st));
+    if (n_services) memcpy(verdicts, hs + kOffVerdicts, n_services * sizeof(fm_verdict));
+    return FM_OK;
+  }
   fm_result *r = new (std::nothrow) fm_result;
   if (!r) return FM_E_NOMEM;
   std::vector<cudaEvent_t> evs;

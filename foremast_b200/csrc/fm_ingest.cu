@@ -10,11 +10,23 @@
 // allocation, values written straight into the caller's float array, label objects returned as
 // byte spans.  Sample strings go string -> double -> float (the same two roundings as Python's
 // float() followed by a cast), "NaN" / "+Inf" / "-Inf" are kept as such and dropped later by
-// fm_batch_add_series (a gap).  Host code only: nothing here touches the GPU.
+// fm_batch_add_series (a gap).
+//
+// Timestamps matter: query_range answers on the grid start + k*step and simply OMITS a scrape that is
+// missing, while everything downstream is index-based (Wilcoxon pairs sample i with sample i, the
+// Holt-Winters phase is index mod period, anomaly times are t0 + index*step).  So every timestamp is
+// read (integer fast path), the step is the smallest gap between neighbours, and a series reports how
+// many grid slots it lacks; with FM_PROM_GRID the samples are PLACED on the grid -- holes are NaN, or
+// the previous sample with FM_PROM_FILL -- so that index and time stay the same thing.
+// fm_batch_add_prometheus / _many feed response bodies straight into a batch (no Python, no DOM),
+// the latter parsing on a thread pool.  Host code only: nothing here touches the GPU.
+#include <atomic>
 #include <charconv>
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <thread>
+#include <vector>
 
 #include "../../include/foremast_gpu.h"
 
@@ -56,6 +68,30 @@ struct Scan {
     p = r.ptr;
     return true;
   }
+  // a timestamp: unix seconds, usually an integer or with a few decimals ("1550000060", "1550000060.123")
+  bool timestamp(double *out) {
+    ws();
+    const char *q = p;
+    uint64_t ip = 0;
+    int nd = 0;
+    while (q < end && *q >= '0' && *q <= '9' && nd < 15) { ip = ip * 10 + (uint64_t)(*q - '0'); ++q; ++nd; }
+    if (nd > 0 && q < end && (*q == ',' || *q == ' ')) { *out = (double)ip; p = q; return true; }
+    return number(out);
+  }
+  // a sample value: a quoted number ("0.166", "NaN"); no escapes expected, so the closing quote is a memchr away
+  bool quoted(const char **s, size_t *n) {
+    ws();
+    if (p >= end || *p != '"') return ok = false;
+    const char *q = p + 1;
+    const char *e = static_cast<const char *>(memchr(q, '"', (size_t)(end - q)));
+    if (!e) return ok = false;
+    if (memchr(q, '\\', (size_t)(e - q))) return string(s, n);
+    *s = q;
+    *n = (size_t)(e - q);
+    p = e + 1;
+    return true;
+  }
+  bool skip_quoted() { const char *s; size_t n; return quoted(&s, &n); }
   bool skip_number() {  // a JSON number, not converted
     ws();
     const char *q = p;
@@ -130,14 +166,17 @@ double sample_value(const char *s, size_t n) {
   return std::numeric_limits<double>::quiet_NaN();  // unparsable sample = gap
 }
 
-}  // namespace
-
-extern "C" int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_prom_series *series, uint32_t series_cap,
-                                          uint32_t *n_series, float *values, uint64_t values_cap, uint64_t *n_values) {
-  if (!json || !n_series || !n_values) return FM_E_INVALID;
+// One pass over the response.  Series descriptors go to `series` (up to series_cap), samples to `values`
+// (up to values_cap); counts keep running past the capacities so that the caller learns what to allocate.
+// flags: FM_PROM_GRID places samples at round((ts - t0) / step), step = step_hint if > 0, else the smallest
+// gap of the series (found by a first look at its timestamps); FM_PROM_FILL fills holes with the previous
+// sample instead of NaN.
+int walk_matrix(const char *json, uint64_t len, uint32_t flags, double step_hint, fm_prom_series *series, uint32_t series_cap,
+                uint32_t *n_series, float *values, uint64_t values_cap, uint64_t *n_values) {
   Scan sc{json, json + len, json};
   uint32_t ns = 0;
   uint64_t nv = 0;
+  const bool grid = (flags & FM_PROM_GRID) != 0, fill = (flags & FM_PROM_FILL) != 0;
   auto finish = [&](int rc) { *n_series = ns; *n_values = nv; return rc; };
   if (!sc.eat('{')) return finish(FM_E_INVALID);
   // top level: find "data"
@@ -171,23 +210,74 @@ extern "C" int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_pro
                 cur.metric_len = (uint64_t)(sc.p - m0);
               } else if (key_is(k, kn, "values")) {
                 if (!sc.eat('[')) return finish(FM_E_INVALID);
-                double t_prev = 0.0;
+                // The step of the grid is the hint (the query's own step) or, without one, the smallest gap of
+                // the series -- which takes a first look at its timestamps, but only when samples are to be placed.
+                double step = step_hint > 0.0 ? step_hint : 0.0;
+                if (grid && !(step > 0.0)) {
+                  Scan look = sc;
+                  double t_prev = 0.0;
+                  uint32_t seen = 0;
+                  while (look.ok) {
+                    if (look.eat(']')) break;
+                    double ts = 0.0;
+                    if (!look.eat('[') || !look.timestamp(&ts) || !look.eat(',') || !look.skip_quoted() || !look.eat(']'))
+                      return finish(FM_E_INVALID);
+                    const double gap = ts - t_prev;
+                    if (seen && gap > 0.0 && (step == 0.0 || gap < step)) step = gap;
+                    t_prev = ts;
+                    ++seen;
+                    look.eat(',');
+                  }
+                  if (!look.ok) return finish(FM_E_INVALID);
+                }
+                const bool place = grid && step > 0.0;
+                double t0 = 0.0, t_prev = 0.0, min_gap = 0.0;
+                uint32_t count = 0;
+                bool ordered = true;
+                uint64_t at = 0;  // next grid slot to write (place)
+                float last_v = std::numeric_limits<float>::quiet_NaN();
                 while (sc.ok) {
                   if (sc.eat(']')) break;
                   double ts = 0.0;
                   const char *vs; size_t vn;
-                  if (!sc.eat('[')) return finish(FM_E_INVALID);
-                  // only the first two timestamps carry information (t0 and the step); the rest are skipped
-                  if (cur.n_values < 2 ? !sc.number(&ts) : !sc.skip_number()) return finish(FM_E_INVALID);
-                  if (!sc.eat(',') || !sc.string(&vs, &vn) || !sc.eat(']')) return finish(FM_E_INVALID);
-                  if (cur.n_values == 0) cur.t0 = ts;
-                  else if (cur.n_values == 1) cur.step = ts - t_prev;
+                  if (!sc.eat('[') || !sc.timestamp(&ts) || !sc.eat(',') || !sc.quoted(&vs, &vn) || !sc.eat(']'))
+                    return finish(FM_E_INVALID);
+                  if (count == 0) t0 = ts;
+                  else {
+                    const double gap = ts - t_prev;
+                    if (!(gap > 0.0)) ordered = false;
+                    else if (min_gap == 0.0 || gap < min_gap) min_gap = gap;
+                  }
                   t_prev = ts;
-                  if (values && nv < values_cap) values[nv] = (float)sample_value(vs, vn);
+                  ++count;
+                  const float v = (float)sample_value(vs, vn);
+                  if (place && ordered) {
+                    const double rel = (ts - t0) / step;
+                    if (rel > 64.0 * count + 1024.0) return finish(FM_E_INVALID);  // nonsense timestamps
+                    uint64_t slot = (uint64_t)llround(rel);
+                    if (slot < at) slot = at;  // two samples rounding onto one slot: keep both, in order
+                    for (; at < slot; ++at, ++nv)
+                      if (values && nv < values_cap) values[nv] = fill ? last_v : std::numeric_limits<float>::quiet_NaN();
+                  }
+                  if (values && nv < values_cap) values[nv] = v;
+                  if (std::isfinite(v)) last_v = v;
                   ++nv;
-                  ++cur.n_values;
+                  ++at;
                   sc.eat(',');
                 }
+                if (!(step > 0.0)) step = min_gap;
+                cur.t0 = t0;
+                cur.step = step;
+                // grid slots up to the last sample that have no sample of their own
+                cur.reserved = 0;
+                if (!ordered) cur.reserved = 0xFFFFFFFFu;
+                else if (count > 1 && step > 0.0) {
+                  const double span = (t_prev - t0) / step;
+                  if (span > 64.0 * count + 1024.0) return finish(FM_E_INVALID);
+                  const uint64_t slots = (uint64_t)llround(span) + 1;
+                  cur.reserved = slots > count ? (uint32_t)(slots - count) : 0u;
+                }
+                cur.n_values = (uint32_t)(nv - cur.first_value);
               } else {
                 sc.skip_value();
               }
@@ -211,3 +301,118 @@ extern "C" int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_pro
   if (ns > series_cap || nv > values_cap) return finish(FM_E_RANGE);  // counts tell the caller what to allocate
   return finish(FM_OK);
 }
+
+// a whole response into vectors (sized by a counting pass)
+struct Parsed {
+  std::vector<fm_prom_series> series;
+  std::vector<float> values;
+  int rc = FM_OK;
+};
+void parse_into(const char *json, uint64_t len, uint32_t flags, double step_hint, Parsed *out) {
+  out->series.clear();
+  out->values.clear();
+  if (!json || len == 0) { out->rc = FM_OK; return; }  // a job without this query
+  uint32_t ns = 0;
+  uint64_t nv = 0;
+  int rc = walk_matrix(json, len, flags, step_hint, nullptr, 0, &ns, nullptr, 0, &nv);
+  if (rc != FM_OK && rc != FM_E_RANGE) { out->rc = rc; return; }
+  out->series.resize(ns);
+  out->values.resize(nv);
+  out->rc = walk_matrix(json, len, flags, step_hint, out->series.data(), ns, &ns, out->values.data(), nv, &nv);
+}
+
+// The worker's pairing of one job alias (foremast_b200/brain.py::build_units): one unit per CURRENT series
+// (new pod); its baseline is the baseline series of the same rank (old pod i vs new pod i, the last one if
+// there are fewer), its history the first historical series (the app-level query,
+// foremast-barrelman/pkg/client/metrics/metricsquery.go:79-99).
+int add_units(fm_batch *b, const fm_series_meta *meta, const Parsed &h, const Parsed &bs, const Parsed &c, uint32_t *n_added) {
+  *n_added = 0;
+  const float *hv = h.series.empty() ? nullptr : h.values.data() + h.series[0].first_value;
+  const uint32_t hn = h.series.empty() ? 0u : h.series[0].n_values;
+  for (size_t i = 0; i < c.series.size(); ++i) {
+    const float *bv = nullptr;
+    uint32_t bn = 0;
+    if (!bs.series.empty()) {
+      const fm_prom_series &s = bs.series[std::min(i, bs.series.size() - 1)];
+      bv = bs.values.data() + s.first_value;
+      bn = s.n_values;
+    }
+    const fm_prom_series &s = c.series[i];
+    const int rc = fm_batch_add_series(b, meta, hv, hn, bv, bn, c.values.data() + s.first_value, s.n_values);
+    if (rc) return rc;
+    ++*n_added;
+  }
+  return FM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_prom_series *series, uint32_t series_cap,
+                               uint32_t *n_series, float *values, uint64_t values_cap, uint64_t *n_values) {
+  if (!json || !n_series || !n_values) return FM_E_INVALID;
+  return walk_matrix(json, len, 0u, 0.0, series, series_cap, n_series, values, values_cap, n_values);
+}
+
+int fm_parse_prometheus_matrix_grid(const char *json, uint64_t len, uint32_t flags, double step_hint, fm_prom_series *series,
+                                    uint32_t series_cap, uint32_t *n_series, float *values, uint64_t values_cap,
+                                    uint64_t *n_values) {
+  if (!json || !n_series || !n_values || (flags & ~(FM_PROM_GRID | FM_PROM_FILL))) return FM_E_INVALID;
+  return walk_matrix(json, len, flags, step_hint, series, series_cap, n_series, values, values_cap, n_values);
+}
+
+int fm_batch_add_prometheus(fm_batch *b, const fm_prom_job *job, uint32_t flags, uint32_t *n_units_added) {
+  uint32_t n = 0;
+  if (n_units_added) *n_units_added = 0;
+  if (!b || !job || (flags & ~(FM_PROM_GRID | FM_PROM_FILL))) return FM_E_INVALID;
+  Parsed h, bs, c;
+  parse_into(job->hist_json, job->hist_len, flags, job->step, &h);
+  parse_into(job->base_json, job->base_len, flags, job->step, &bs);
+  parse_into(job->cur_json, job->cur_len, flags, job->step, &c);
+  if (h.rc || bs.rc || c.rc) return FM_E_INVALID;
+  const int rc = add_units(b, &job->meta, h, bs, c, &n);
+  if (n_units_added) *n_units_added = n;
+  return rc;
+}
+
+int fm_batch_add_prometheus_many(fm_batch *b, const fm_prom_job *jobs, uint32_t n_jobs, uint32_t flags, uint32_t n_threads,
+                                 uint32_t *units_per_job) {
+  if (!b || (n_jobs && !jobs) || (flags & ~(FM_PROM_GRID | FM_PROM_FILL))) return FM_E_INVALID;
+  struct Job3 { Parsed h, b, c; };
+  std::vector<Job3> parsed(n_jobs);
+  if (n_threads == 0) n_threads = std::max(1u, std::thread::hardware_concurrency());
+  n_threads = std::min<uint32_t>(n_threads, std::max<uint32_t>(n_jobs, 1));
+  std::atomic<uint32_t> next{0};
+  auto work = [&]() {  // the scanner is reentrant: one response at a time per thread, results in job order
+    for (uint32_t i = next.fetch_add(1); i < n_jobs; i = next.fetch_add(1)) {
+      parse_into(jobs[i].hist_json, jobs[i].hist_len, flags, jobs[i].step, &parsed[i].h);
+      parse_into(jobs[i].base_json, jobs[i].base_len, flags, jobs[i].step, &parsed[i].b);
+      parse_into(jobs[i].cur_json, jobs[i].cur_len, flags, jobs[i].step, &parsed[i].c);
+    }
+  };
+  try {
+    std::vector<std::thread> pool;
+    for (uint32_t t = 1; t < n_threads; ++t) pool.emplace_back(work);
+    work();
+    for (auto &t : pool) t.join();
+  } catch (...) {
+    return FM_E_NOMEM;
+  }
+  // append in job order: the unit numbering does not depend on the thread schedule.  A job whose responses do
+  // not parse adds no units (the worker marks it preprocess_failed) and does not stop the others.
+  int first_rc = FM_OK;
+  for (uint32_t i = 0; i < n_jobs; ++i) {
+    uint32_t n = 0;
+    if (parsed[i].h.rc || parsed[i].b.rc || parsed[i].c.rc) {
+      if (units_per_job) units_per_job[i] = 0xFFFFFFFFu;
+      continue;
+    }
+    const int rc = add_units(b, &jobs[i].meta, parsed[i].h, parsed[i].b, parsed[i].c, &n);
+    if (units_per_job) units_per_job[i] = n;
+    if (rc && first_rc == FM_OK) first_rc = rc;
+  }
+  return first_rc;
+}
+
+}  // extern "C"

@@ -232,12 +232,41 @@ void fm_host_free(fm_ctx *ctx, void *p);
  * cycle has thousands of them. */
 typedef struct fm_prom_series {
   uint64_t metric_off, metric_len;
-  double t0, step;
+  double t0, step;             /* first timestamp; smallest gap between neighbouring samples (or the hint) */
   uint64_t first_value;
-  uint32_t n_values, reserved;
+  uint32_t n_values;
+  uint32_t reserved;           /* grid slots t0 + k*step up to the last sample that have NO sample (missing
+                                  scrapes; 0 = the series is regular), 0xFFFFFFFF if timestamps do not ascend */
 } fm_prom_series;
 int fm_parse_prometheus_matrix(const char *json, uint64_t len, fm_prom_series *series, uint32_t series_cap,
                                uint32_t *n_series, float *values, uint64_t values_cap, uint64_t *n_values);
+/* query_range omits a missing scrape instead of sending NaN, while the scorers are index-based (Wilcoxon
+ * pairs sample i with sample i, the Holt-Winters phase is index mod period, anomaly times are t0 + i*step,
+ * foremast-barrelman/pkg/client/metrics/metricsquery.go:63).  With FM_PROM_GRID every sample is placed at
+ * round((ts - t0) / step) -- step_hint (the `step` of the query URL, prometheushelper.go:13-43) or, when
+ * <= 0, the smallest gap of the series -- and the holes are NaN (dropped later = the old behaviour, but now
+ * visible in `reserved`), or the previous sample with FM_PROM_FILL, which keeps index and time aligned. */
+#define FM_PROM_GRID (1u << 0)
+#define FM_PROM_FILL (1u << 1)
+int fm_parse_prometheus_matrix_grid(const char *json, uint64_t len, uint32_t flags, double step_hint, fm_prom_series *series,
+                                    uint32_t series_cap, uint32_t *n_series, float *values, uint64_t values_cap,
+                                    uint64_t *n_values);
+/* Response bodies straight into a batch, no host language in the loop: the three query_range answers of ONE
+ * job alias (historicalConfig / baselineConfig / currentConfig entry, main.go:50-81; any may be NULL) become
+ * one unit per current series -- baseline series of the same rank, first historical series -- exactly the
+ * pairing of the worker (foremast_b200/brain.py::build_units).  _many parses n_jobs such triples on a thread
+ * pool (n_threads = 0: all cores; the scanner is reentrant) and appends them in job order; units_per_job[i]
+ * = units added for job i, or 0xFFFFFFFF if its responses do not parse (the others are still added). */
+typedef struct fm_prom_job {
+  fm_series_meta meta;
+  uint32_t reserved;
+  double step;                 /* query step in seconds, <= 0: take it from the data */
+  const char *hist_json, *base_json, *cur_json;
+  uint64_t hist_len, base_len, cur_len;
+} fm_prom_job;
+int fm_batch_add_prometheus(fm_batch *b, const fm_prom_job *job, uint32_t flags, uint32_t *n_units_added);
+int fm_batch_add_prometheus_many(fm_batch *b, const fm_prom_job *jobs, uint32_t n_jobs, uint32_t flags, uint32_t n_threads,
+                                 uint32_t *units_per_job);
 
 /* Incremental ingest of one job's series: what the brain does after fetching the three
  * query_range matrices named by currentConfig / baselineConfig / historicalConfig

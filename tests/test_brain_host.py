@@ -105,6 +105,39 @@ def test_native_matrix_scanner_matches_json_module():
             brain.parse_matrix(bad)
 
 
+def test_missing_scrapes_are_seen_and_regridded():
+    """query_range omits a missing scrape.  The scanner reports the holes (`reserved`), and with PROM_GRID the
+    samples sit at round((ts - t0) / step): index i IS time t0 + i*step again ([10, 70, 190] used to
+    parse as three uniform samples)."""
+    def body(points):
+        return json.dumps({"status": "success", "data": {"resultType": "matrix", "result": [
+            {"metric": {"pod": "a"}, "values": [[t, str(v)] for t, v in points]}]}}).encode()
+    pts = [(10, 1.0), (70, 2.0), (190, 4.0), (250, 5.0), (490, 9.0)]
+    series, values = brain.parse_matrix_series(body(pts))
+    assert int(series[0]["n_values"]) == 5 and float(series[0]["t0"]) == 10.0 and float(series[0]["step"]) == 60.0
+    assert int(series[0]["reserved"]) == 4                      # slots 130, 310, 370, 430 have no sample
+    assert list(values) == [1.0, 2.0, 4.0, 5.0, 9.0]            # plain mode keeps the samples as they came
+    series, values = brain.parse_matrix_series(body(pts), abi.PROM_GRID)
+    assert int(series[0]["n_values"]) == 9
+    assert np.array_equal(np.isnan(values), [False, False, True, False, False, True, True, True, False])
+    series, values = brain.parse_matrix_series(body(pts), abi.PROM_GRID | abi.PROM_FILL)
+    assert list(values) == [1.0, 2.0, 2.0, 4.0, 5.0, 5.0, 5.0, 5.0, 9.0]
+    # the first pair spans a gap: the smallest gap is the step, not the first one ...
+    series, values = brain.parse_matrix_series(body([(0, 1.0), (120, 3.0), (180, 4.0), (240, 5.0)]), abi.PROM_GRID | abi.PROM_FILL)
+    assert float(series[0]["step"]) == 60.0 and list(values) == [1.0, 1.0, 3.0, 4.0, 5.0]
+    # ... and a step hint from the query URL settles it when every gap is a multiple
+    series, values = brain.parse_matrix_series(body([(0, 1.0), (120, 3.0), (240, 5.0)]), abi.PROM_GRID, 60.0)
+    assert int(series[0]["reserved"]) == 2 and int(series[0]["n_values"]) == 5
+    # regular series: nothing changes, fractional timestamps included
+    reg = [(1550000000.123 + 60 * i, i) for i in range(50)]
+    s0, v0 = brain.parse_matrix_series(body(reg))
+    s1, v1 = brain.parse_matrix_series(body(reg), abi.PROM_GRID | abi.PROM_FILL)
+    assert int(s0[0]["reserved"]) == 0 and v0.tobytes() == v1.tobytes()
+    # timestamps that go backwards are flagged, never re-gridded
+    s2, v2 = brain.parse_matrix_series(body([(100, 1.0), (40, 2.0), (160, 3.0)]), abi.PROM_GRID)
+    assert int(s2[0]["reserved"]) == 0xFFFFFFFF and list(v2) == [1.0, 2.0, 3.0]
+
+
 def test_native_matrix_scanner_is_reentrant():
     """One response per thread (the worker's fan-out): same results as serially, and the calls really
     run side by side (ctypes drops the GIL)."""
@@ -142,3 +175,33 @@ def test_exporter_series_names_match_dashboard():
     assert 'foremastbrain:namespace_app_pod_http_server_requests_errors_5xx_anomaly{exported_namespace="dev",app="demo"} 1550001260' in txt
     assert re.match(r"^foremastbrain.*", txt.splitlines()[1])   # custom-metrics-config-map.yaml:27
     assert exporter.exposition("m", "n", "a") == ""
+
+
+def test_hpa_score_rule():
+    """docs/dynamic_autoscaling.md:31-55: > 50 only for a rewarded scale-up, < 50 only for a rewarded scale-down."""
+    d = lambda tps, lat: [{"metricType": "tps", "current": tps, "upper": 120.0, "lower": 80.0},  # noqa: E731
+                          {"metricType": "latency", "current": lat, "upper": 300.0, "lower": 0.0}]
+    assert brain.hpa_score(d(100, 100))[0] == 50            # load inside its band
+    assert brain.hpa_score(d(140, 100))[0] == 50            # load up but the SLA holds: scaling up is not rewarded
+    assert brain.hpa_score(d(140, 400))[0] == 75            # load up half a band width and latency out of its band
+    assert brain.hpa_score(d(500, 400))[0] == 100
+    assert brain.hpa_score(d(60, 100))[0] == 25             # load down, SLA holds: scale down
+    assert brain.hpa_score(d(60, 400))[0] == 50             # load down but latency violated: no reward for scaling down
+    assert brain.hpa_score([{"metricType": "cpu", "current": 1, "upper": 2, "lower": 0}])[0] == 50
+
+
+def test_metrics_endpoint_serves_bands_and_hpa_score():
+    import urllib.request
+    from foremast_b200 import exporter
+    srv = exporter.MetricsServer(port=0)
+    try:
+        srv.set_band("dev", "demo", "namespace_app_pod_http_server_requests_latency", upper=310.5, lower=0.0, anomaly_ts=[1550000060])
+        srv.set_hpa_score("dev", "demo", 75)
+        page = urllib.request.urlopen(f"http://127.0.0.1:{srv.port}/metrics", timeout=5).read().decode()
+        assert 'foremastbrain:namespace_app_pod_http_server_requests_latency_upper{exported_namespace="dev",app="demo"} 310.5' in page
+        assert 'foremastbrain:namespace_app_pod_http_server_requests_latency_anomaly{exported_namespace="dev",app="demo"} 1550000060' in page
+        assert 'foremastbrain:namespace_app_per_pod:hpa_score{exported_namespace="dev",app="demo"} 75' in page
+        import re
+        assert all(re.match(r"^(#|foremastbrain[:\w]*\{)", ln) for ln in page.strip().split("\n"))  # adapter: ^foremastbrain.*
+    finally:
+        srv.close()

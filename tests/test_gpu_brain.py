@@ -53,3 +53,116 @@ def test_demo_job_goes_unhealthy_then_healthy(golden_dir):
         # broken store -> preprocess_failed
         doc["currentConfig"] = "cpu== http://prom/missing"
         assert w.process(doc)["status"] == "preprocess_failed"
+
+
+def body(series, t0=1550000000, step=60, drop=()):
+    """query_range response body (bytes); sample indices in `drop` are missing scrapes (simply absent)."""
+    return json.dumps({"status": "success", "data": {"resultType": "matrix", "result": [
+        {"metric": {"pod": f"pod-{i}"}, "values": [[t0 + k * step, repr(float(v))] for k, v in enumerate(s) if k not in drop]}
+        for i, s in enumerate(series)]}}).encode()
+
+
+def test_response_bodies_straight_into_a_batch():
+    """fm_batch_add_prometheus_many: the three bodies of every job alias become units with the worker's pairing,
+    parsed on a thread pool, identical to the per-series path (fm_batch_add_series) on the same data; missing
+    scrapes are re-gridded (filled) so that indices stay times; a malformed body fails only its own job."""
+    from foremast_b200.api import Context
+    rng = np.random.default_rng(8)
+    jobs, want_units, want_meta = [], [], []
+    for j in range(23):
+        nb, nc = int(rng.integers(1, 4)), int(rng.integers(1, 5))
+        hist = rng.normal(50, 5, int(rng.integers(0, 400))).astype(np.float32)
+        base = [rng.normal(50, 5, int(rng.integers(5, 80))).astype(np.float32) for _ in range(nb)]
+        cur = [rng.normal(50, 5, int(rng.integers(5, 80))).astype(np.float32) for _ in range(nc)]
+        jobs.append((j, 1 + j % 8, 60.0, body([hist]) if hist.size else None, body(base), body(cur)))
+        for i, c in enumerate(cur):
+            want_units.append((hist, base[min(i, nb - 1)], c))
+            want_meta.append((j, 1 + j % 8))
+    with Context(0) as ctx:
+        b, per = ctx.batch_from_prometheus(jobs, threads=4)
+        ref = ctx.batch_from_units(want_units, service_id=[m[0] for m in want_meta], metric_type=[m[1] for m in want_meta])
+        hb, hr = b.download(), ref.download()
+        assert int(per.sum()) == len(want_units)
+        for f in ("values", "offsets", "seg_lens", "service_id", "metric_type"):
+            assert np.array_equal(getattr(hb, f), getattr(hr, f)), f
+        b.free()
+        ref.free()
+        # a missing scrape: sample 3 of the current window is absent -> with GRID|FILL its slot holds sample 2 again
+        cur = np.arange(10, dtype=np.float32)
+        b, per = ctx.batch_from_prometheus([(0, 1, 60.0, None, body([cur]), body([cur], drop={3}))])
+        seg = b.download().segments(0)
+        assert list(seg[2]) == [0, 1, 2, 2, 4, 5, 6, 7, 8, 9]
+        b.free()
+        b, per = ctx.batch_from_prometheus([(0, 1, 60.0, None, body([cur]), body([cur], drop={3}))], flags=0)
+        assert list(b.download().segments(0)[2]) == [0, 1, 2, 4, 5, 6, 7, 8, 9]  # plain mode: samples as they came
+        b.free()
+        # one broken body among good ones
+        b, per = ctx.batch_from_prometheus([(0, 1, 60.0, None, body([cur]), body([cur])),
+                                            (1, 1, 60.0, None, b'{"data":{"result":[{"values":[[1,2]]}]}}', body([cur])),
+                                            (2, 1, 60.0, None, body([cur]), body([cur, cur]))])
+        assert list(per) == [1, -1, 2] and b.info()["n_units"] == 3
+        b.free()
+
+
+def test_worker_batches_jobs_and_owns_the_state_machine():
+    """500 mixed job documents through ONE scoring pass give the same per-job status / reason / anomalyInfo as
+    500 single calls; run_once drives the store through the brain's status transitions
+    (converter.go:12-25), takes over stuck jobs after MAX_STUCK_IN_SECONDS and writes hpalogs for hpa jobs."""
+    from foremast_b200.api import Context, default_params
+    rng = np.random.default_rng(21)
+    store_bodies, docs = {}, []
+    t_end = 1550000000 + 60 * 40
+    for j in range(500):
+        kind = j % 5
+        n_pods = 1 + j % 3
+        base = [rng.normal(100, 4, 40) for _ in range(n_pods)]
+        cur = [rng.normal(100, 4, 40) for _ in range(n_pods)]
+        if kind == 1:
+            cur[0][7] = 400.0                       # a spike -> unhealthy
+        if kind == 2:
+            cur = [c + 30 for c in cur]             # a level shift
+        lat_b, lat_c = [rng.normal(200, 10, 40)], [rng.normal(200, 10, 40)]
+        if kind == 4:
+            lat_c[0][-1] = 900.0
+        for name, series in (("b_tps", base), ("c_tps", cur), ("b_lat", lat_b), ("c_lat", lat_c)):
+            store_bodies[f"http://prom/{j}/{name}"] = body(series)
+        doc = {"id": f"job-{j}", "appName": f"app{j}", "strategy": ["canary", "rollover", "continuous", "canary", "hpa"][kind],
+               "status": "initial", "startTimeUnix": 1550000000, "endTimeUnix": t_end if kind != 3 else t_end + 10_000,
+               "baselineConfig": f"tps== http://prom/{j}/b_tps || latency== http://prom/{j}/b_lat",
+               "currentConfig": f"tps== http://prom/{j}/c_tps || latency== http://prom/{j}/c_lat"}
+        if j == 77:
+            doc["currentConfig"] = ""               # no current metric -> unknown
+        if j == 78:
+            doc["currentConfig"] = "tps== http://prom/missing"   # fetch fails
+        docs.append(doc)
+    p = default_params()
+    p.rules[abi.MT_TPS].threshold, p.rules[abi.MT_TPS].bound = 4.0, abi.BOUND_BOTH
+    with Context(0) as ctx:
+        w = brain.BrainWorker(ctx, lambda url: store_bodies[url], p, clock=lambda: float(t_end + 100))
+        many = w.process_many(docs)
+        singles = [w.process(d) for d in docs]
+        assert len(many) == 500
+        for a, b_ in zip(many, singles):
+            for k in ("status", "reason", "anomalyInfo"):
+                assert a.get(k) == b_.get(k), k
+        st = [m["status"] for m in many]
+        assert st[77] == "completed_unknown" and st[78] == "preprocess_failed"
+        assert st.count("completed_unhealth") >= 150 and st.count("completed_health") >= 60
+        assert st.count("postprocess_inprogress") > 0          # kind 3: endTime not reached yet
+        assert all("hpalog" in m for j, m in enumerate(many) if j % 5 == 4 and j != 78)
+        hl = many[4]["hpalog"]["hpalog"]
+        assert 0 <= hl["hpascore"] <= 100 and {d["metricType"] for d in hl["details"]} == {"tps", "latency"}
+        # ---- the store loop
+        store = brain.DictStore(docs[:50])
+        store.update("job-3", {"status": "preprocess_inprogress", "modified_at": float(t_end + 100 - 30)})    # someone else, recently
+        store.update("job-8", {"status": "preprocess_inprogress", "modified_at": float(t_end + 100 - 500)})   # stuck
+        assert w.run_once(store) == 49
+        assert store.docs["job-3"]["status"] == "preprocess_inprogress"                  # left alone
+        assert store.docs["job-8"]["status"] == many[8]["status"]                        # taken over and finished
+        for j in range(50):
+            if j != 3:
+                assert store.docs[f"job-{j}"]["status"] == many[j]["status"], j
+        assert len(store.hpalogs) == 10 and store.hpalogs[0]["job_id"] == "job-4"
+        # postprocess_inprogress jobs are picked up again on the next cycle, finished ones are not
+        again = w.run_once(store)
+        assert again == sum(1 for j in range(50) if j != 3 and many[j]["status"] == "postprocess_inprogress")
