@@ -314,7 +314,7 @@ def run_ours(args):
                 for i in range(n_series)]}}).encode()
         hb, cb = prom_body(1, 1380, 1), prom_body(8, 60, 2)
         n_jobs = 10_000
-        jobs = [(j // 10, abi.MT_CPU, 60.0, hb, None, cb) for j in range(n_jobs)]
+        jobs = ctx.prom_jobs([(j // 10, abi.MT_CPU, 60.0, hb, None, cb) for j in range(n_jobs)])  # the C array, made once
         json_mb = n_jobs * (len(hb) + len(cb)) / 1e6
         q = bench_params(default_params()); q.algorithms = abi.ALG_EWMA | abi.ALG_DES; q.pairwise = abi.PW_NONE
         ts_pack, ts_total = [], []
@@ -331,7 +331,7 @@ def run_ours(args):
                 ts_pack.append(t1 - t0)
                 ts_total.append(t2 - t0)
         t0 = time.perf_counter()
-        bb, _ = ctx.batch_from_prometheus(jobs[:n_jobs // 16], threads=1)
+        bb, _ = ctx.batch_from_prometheus((jobs[0], n_jobs // 16, jobs[2]), threads=1)
         one_thread_s = time.perf_counter() - t0
         bb.free()
         other["ingest_prometheus_json_cfg2_shape"] = {

@@ -140,20 +140,27 @@ class Context:
         self._check(self._L.fm_batch_seal(h))
         return b
 
-    def batch_from_prometheus(self, jobs, flags=abi.PROM_GRID | abi.PROM_FILL, threads=0):
-        """Response bodies -> sealed batch without Python in the loop (fm_batch_add_prometheus_many).
-        jobs = [(service_id, metric_type, step_seconds, hist_body, base_body, cur_body), ...] (bodies are
-        bytes or None).  Returns (batch, units_per_job); a job whose bodies do not parse gets -1 units."""
+    @staticmethod
+    def prom_jobs(jobs):
+        """[(service_id, metric_type, step_seconds, hist_body, base_body, cur_body), ...] (bodies: bytes or
+        None) -> the fm_prom_job array fm_batch_add_prometheus_many takes, ready to be used many times."""
         n = len(jobs)
         arr = (abi.PromJob * max(n, 1))()
         keep = []
         for i, (sid, mt, step, hb, bb, cb) in enumerate(jobs):
             j = arr[i]
             j.meta.service_id, j.meta.metric_type, j.step = int(sid), int(mt), float(step)
-            for name, body in (("hist", hb), ("base", bb), ("cur", cb)):
-                keep.append(body)
-                setattr(j, name + "_json", body)
-                setattr(j, name + "_len", len(body) if body else 0)
+            j.hist_json, j.hist_len = hb, len(hb) if hb else 0
+            j.base_json, j.base_len = bb, len(bb) if bb else 0
+            j.cur_json, j.cur_len = cb, len(cb) if cb else 0
+            keep.append((hb, bb, cb))
+        return arr, n, keep
+
+    def batch_from_prometheus(self, jobs, flags=abi.PROM_GRID | abi.PROM_FILL, threads=0):
+        """Response bodies -> sealed batch without Python in the loop (fm_batch_add_prometheus_many).
+        jobs = a list of (service_id, metric_type, step_seconds, hist_body, base_body, cur_body), or what
+        prom_jobs() made of one.  Returns (batch, units_per_job); a job whose bodies do not parse gets -1."""
+        arr, n, _keep = jobs if isinstance(jobs, tuple) else self.prom_jobs(jobs)
         h = C.c_void_p()
         self._check(self._L.fm_batch_begin(self._h, n, 0, C.byref(h)))
         b = Batch(self, h)

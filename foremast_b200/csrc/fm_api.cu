@@ -53,6 +53,15 @@ constexpr uint64_t kOffVerdicts = kOffUpts + a16((kArenaUnits + 1) * 4);
 constexpr uint64_t kArenaBytes = kOffVerdicts + a16((kArenaServices + 1) * sizeof(fm_verdict));
 }  // namespace
 
+// std::allocator value-initialises on resize(); the bulk ingest path reserves hundreds of MB that its threads then
+// fill completely, so zeroing them first (one thread, fresh pages) was a third of its time
+template <class T>
+struct DefaultInitAlloc : std::allocator<T> {
+  template <class U> struct rebind { using other = DefaultInitAlloc<U>; };
+  template <class U> void construct(U *p) noexcept { ::new (static_cast<void *>(p)) U; }
+  template <class U, class... A> void construct(U *p, A &&...a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+
 struct fm_batch {
   fm_ctx *ctx = nullptr;
   bool sealed = false, owns = true;
@@ -64,7 +73,7 @@ struct fm_batch {
   uint32_t *d_seg = nullptr, *d_sid = nullptr;
   uint8_t *d_mt = nullptr;
   // host staging of the incremental path
-  std::vector<float> h_values;
+  std::vector<float, DefaultInitAlloc<float>> h_values;
   std::vector<int64_t> h_offsets;
   std::vector<uint32_t> h_seg, h_sid;
   std::vector<uint8_t> h_mt;
@@ -464,6 +473,33 @@ int fm_batch_add_series(fm_batch *b, const fm_series_meta *meta, const float *hi
   return FM_OK;
 }
 
+}  // extern "C"
+
+int fm_batch_reserve_units(fm_batch *b, uint64_t n, const uint32_t *seg_lens, const uint32_t *service_id,
+                           const uint8_t *metric_type, float **values_out, uint64_t *rel_off) {
+  if (!b || (n && (!seg_lens || !values_out || !rel_off))) return FM_E_INVALID;
+  if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
+  try {
+    const uint64_t start = b->h_values.size();
+    uint64_t pos = start;
+    for (uint64_t k = 0; k < n; ++k) {
+      rel_off[k] = pos - start;
+      b->h_offsets.push_back((int64_t)pos);
+      for (int s = 0; s < 3; ++s) b->h_seg.push_back(seg_lens[3 * k + s]);
+      b->h_sid.push_back(service_id ? service_id[k] : 0u);
+      b->h_mt.push_back(metric_type ? metric_type[k] : (uint8_t)0);
+      pos += ((uint64_t)seg_lens[3 * k] + seg_lens[3 * k + 1] + seg_lens[3 * k + 2] + 3) & ~3ull;
+    }
+    b->h_values.resize(pos);  // NOT zero-filled (DefaultInitAlloc): the caller writes every sample and the padding
+    *values_out = b->h_values.data() + start;
+  } catch (...) {
+    return set_err(b->ctx, FM_E_NOMEM, "host staging allocation failed");
+  }
+  return FM_OK;
+}
+
+extern "C" {
+
 int fm_batch_seal(fm_batch *b) {
   if (!b) return FM_E_INVALID;
   if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
@@ -488,7 +524,7 @@ int fm_batch_seal(fm_batch *b) {
     return rc;
   }
   b->sealed = true;
-  std::vector<float>().swap(b->h_values);
+  std::vector<float, DefaultInitAlloc<float>>().swap(b->h_values);
   return FM_OK;
 }
 

@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "../../include/foremast_gpu.h"
+#include "fm_internal.h"
 
 namespace {
 
@@ -306,19 +307,51 @@ int walk_matrix(const char *json, uint64_t len, uint32_t flags, double step_hint
 struct Parsed {
   std::vector<fm_prom_series> series;
   std::vector<float> values;
+  std::vector<uint32_t> finite;  // per series: samples that are finite (the rest are gaps, dropped at ingest, D11)
   int rc = FM_OK;
 };
+
+// dst <- the finite samples of src (with -0.0 stored as +0.0, D11); returns how many
+uint32_t copy_finite(float *dst, const float *src, uint32_t n, uint32_t n_finite) {
+  if (n_finite == n) {
+    for (uint32_t i = 0; i < n; ++i) dst[i] = src[i] + 0.0f;
+    return n;
+  }
+  uint32_t k = 0;
+  for (uint32_t i = 0; i < n; ++i)
+    if (std::isfinite(src[i])) dst[k++] = src[i] + 0.0f;
+  return k;
+}
 void parse_into(const char *json, uint64_t len, uint32_t flags, double step_hint, Parsed *out) {
   out->series.clear();
   out->values.clear();
+  out->finite.clear();
   if (!json || len == 0) { out->rc = FM_OK; return; }  // a job without this query
+  // ONE walk into buffers sized by what the text can hold at most -- a point is at least `[0,"0"],` (8 bytes),
+  // a series at least `{"values":[]},` (14 bytes); re-gridding can add samples the text does not have, and
+  // then the counting walk below sizes the buffers exactly
   uint32_t ns = 0;
   uint64_t nv = 0;
-  int rc = walk_matrix(json, len, flags, step_hint, nullptr, 0, &ns, nullptr, 0, &nv);
-  if (rc != FM_OK && rc != FM_E_RANGE) { out->rc = rc; return; }
+  out->series.resize(len / 14 + 1);
+  out->values.resize(len / 8 + 1);
+  int rc = walk_matrix(json, len, flags, step_hint, out->series.data(), (uint32_t)out->series.size(), &ns, out->values.data(),
+                       out->values.size(), &nv);
+  if (rc == FM_E_RANGE) {
+    out->series.resize(ns);
+    out->values.resize(nv);
+    rc = walk_matrix(json, len, flags, step_hint, out->series.data(), ns, &ns, out->values.data(), nv, &nv);
+  }
+  out->rc = rc;
+  if (rc != FM_OK) return;
   out->series.resize(ns);
   out->values.resize(nv);
-  out->rc = walk_matrix(json, len, flags, step_hint, out->series.data(), ns, &ns, out->values.data(), nv, &nv);
+  out->finite.assign(ns, 0u);
+  for (uint32_t i = 0; i < ns; ++i) {
+    const float *v = out->values.data() + out->series[i].first_value;
+    uint32_t k = 0;
+    for (uint32_t j = 0; j < out->series[i].n_values; ++j) k += std::isfinite(v[j]) ? 1u : 0u;
+    out->finite[i] = k;
+  }
 }
 
 // The worker's pairing of one job alias (foremast_b200/brain.py::build_units): one unit per CURRENT series
@@ -399,20 +432,67 @@ int fm_batch_add_prometheus_many(fm_batch *b, const fm_prom_job *jobs, uint32_t 
   } catch (...) {
     return FM_E_NOMEM;
   }
-  // append in job order: the unit numbering does not depend on the thread schedule.  A job whose responses do
-  // not parse adds no units (the worker marks it preprocess_failed) and does not stop the others.
-  int first_rc = FM_OK;
-  for (uint32_t i = 0; i < n_jobs; ++i) {
-    uint32_t n = 0;
-    if (parsed[i].h.rc || parsed[i].b.rc || parsed[i].c.rc) {
-      if (units_per_job) units_per_job[i] = 0xFFFFFFFFu;
-      continue;
+  // Unit layout in job order (the unit numbering does not depend on the thread schedule), one reservation in
+  // the batch, then the samples are copied in by the same thread pool.  A job whose responses do not parse adds
+  // no units (the worker marks it preprocess_failed) and does not stop the others.
+  std::vector<uint32_t> seg, sid;
+  std::vector<uint8_t> mt;
+  std::vector<uint64_t> first_unit(n_jobs + 1, 0);
+  try {
+    for (uint32_t i = 0; i < n_jobs; ++i) {
+      const Job3 &j = parsed[i];
+      first_unit[i + 1] = first_unit[i];
+      if (j.h.rc || j.b.rc || j.c.rc) {
+        if (units_per_job) units_per_job[i] = 0xFFFFFFFFu;
+        continue;
+      }
+      const uint32_t nh = j.h.series.empty() ? 0u : j.h.finite[0];
+      for (size_t c = 0; c < j.c.series.size(); ++c) {
+        seg.push_back(nh);
+        seg.push_back(j.b.series.empty() ? 0u : j.b.finite[std::min(c, j.b.series.size() - 1)]);
+        seg.push_back(j.c.finite[c]);
+        sid.push_back(jobs[i].meta.service_id);
+        mt.push_back(jobs[i].meta.metric_type);
+      }
+      first_unit[i + 1] += j.c.series.size();
+      if (units_per_job) units_per_job[i] = (uint32_t)j.c.series.size();
     }
-    const int rc = add_units(b, &jobs[i].meta, parsed[i].h, parsed[i].b, parsed[i].c, &n);
-    if (units_per_job) units_per_job[i] = n;
-    if (rc && first_rc == FM_OK) first_rc = rc;
+  } catch (...) {
+    return FM_E_NOMEM;
   }
-  return first_rc;
+  const uint64_t n_units = first_unit[n_jobs];
+  if (n_units == 0) return FM_OK;
+  std::vector<uint64_t> rel(n_units);
+  float *dst = nullptr;
+  const int rc = fm_batch_reserve_units(b, n_units, seg.data(), sid.data(), mt.data(), &dst, rel.data());
+  if (rc) return rc;
+  next = 0;
+  auto fill = [&]() {
+    for (uint32_t i = next.fetch_add(1); i < n_jobs; i = next.fetch_add(1)) {
+      const Job3 &j = parsed[i];
+      for (uint64_t u = first_unit[i]; u < first_unit[i + 1]; ++u) {
+        const size_t c = (size_t)(u - first_unit[i]);
+        float *o = dst + rel[u];
+        if (!j.h.series.empty())
+          o += copy_finite(o, j.h.values.data() + j.h.series[0].first_value, j.h.series[0].n_values, j.h.finite[0]);
+        if (!j.b.series.empty()) {
+          const size_t bi = std::min(c, j.b.series.size() - 1);
+          o += copy_finite(o, j.b.values.data() + j.b.series[bi].first_value, j.b.series[bi].n_values, j.b.finite[bi]);
+        }
+        o += copy_finite(o, j.c.values.data() + j.c.series[c].first_value, j.c.series[c].n_values, j.c.finite[c]);
+        for (uint64_t pad = (uint64_t)(o - (dst + rel[u])); pad & 3; ++pad) *o++ = 0.0f;  // unit starts are 16-byte aligned
+      }
+    }
+  };
+  try {
+    std::vector<std::thread> pool;
+    for (uint32_t t = 1; t < n_threads; ++t) pool.emplace_back(fill);
+    fill();
+    for (auto &t : pool) t.join();
+  } catch (...) {
+    return FM_E_NOMEM;
+  }
+  return FM_OK;
 }
 
 }  // extern "C"
