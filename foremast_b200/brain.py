@@ -443,3 +443,57 @@ class BrainWorker:
         if docs:
             self.process_many(docs, store)
         return len(docs)
+
+
+class ModelCache:
+    """MAX_CACHE_SIZE (foremast-brain/README.md:30, "Max cached model size"): the fitted models the brain keeps
+    between the cycles of continuous / hpa jobs, here Holt-Winters states in HBM (fm_model_fit), looked up by
+    a key (the job id), at most `max_size` of them, the least recently used one freed first.
+
+        cache = ModelCache(ctx, params, max_size=int(env.get("MAX_CACHE_SIZE", 64)))
+        result = cache.score(job_id, make_history_batch, current_batch)
+
+    make_history_batch() is only called on a miss (it fetches the 7-day history); the current batch must
+    hold the same units in the same order as that history (fm_model_score)."""
+
+    def __init__(self, ctx, params, max_size=64):
+        import collections
+        assert max_size >= 1
+        self.ctx, self.params, self.max_size = ctx, params, max_size
+        self._models = collections.OrderedDict()
+        self.hits = self.misses = self.evictions = 0
+
+    def __len__(self):
+        return len(self._models)
+
+    def __contains__(self, key):
+        return key in self._models
+
+    def score(self, key, make_history_batch, current_batch):
+        m = self._models.get(key)
+        if m is None:
+            self.misses += 1
+            hb = make_history_batch()
+            try:
+                m = self.ctx.model_fit(hb, self.params)
+            finally:
+                hb.free()
+            self._models[key] = m
+            while len(self._models) > self.max_size:
+                _, old = self._models.popitem(last=False)
+                old.free()
+                self.evictions += 1
+        else:
+            self.hits += 1
+            self._models.move_to_end(key)
+        return m.score(current_batch)
+
+    def drop(self, key):
+        m = self._models.pop(key, None)
+        if m is not None:
+            m.free()
+
+    def clear(self):
+        for m in self._models.values():
+            m.free()
+        self._models.clear()

@@ -166,3 +166,49 @@ def test_worker_batches_jobs_and_owns_the_state_machine():
         # postprocess_inprogress jobs are picked up again on the next cycle, finished ones are not
         again = w.run_once(store)
         assert again == sum(1 for j in range(50) if j != 3 and many[j]["status"] == "postprocess_inprogress")
+
+
+def test_model_cache_is_keyed_and_capped():
+    """MAX_CACHE_SIZE: models are found by key, a hit fits nothing, the least recently used one is evicted, and a
+    cached model keeps scoring like a fresh pass over history + window (same flags as the oracle)."""
+    from foremast_b200.api import Context
+    from oracle import oracle
+    p = oracle.params_default()
+    p.algorithms, p.pairwise, p.period = abi.ALG_HW, abi.PW_NONE, 64
+    with Context(0) as ctx:
+        cache = brain.ModelCache(ctx, p, max_size=2)
+        jobs = {}
+        for j in range(3):
+            full = oracle.synth(40, 64 * 5, 0, 50, flags=abi.SYNTH_ANOMALIES, seed=100 + j, units_per_service=8)
+            jobs[f"job-{j}"] = (full, [full.segments(u) for u in range(40)])
+        fits = []
+
+        def history(key):
+            def make():
+                fits.append(key)
+                full, units = jobs[key]
+                return ctx.batch_from_units([(h, [], []) for h, _, _ in units], full.service_id, full.metric_type)
+            return make
+
+        def window(key, lo, hi):
+            full, units = jobs[key]
+            return ctx.batch_from_units([([], [], c[lo:hi]) for _, _, c in units], full.service_id, full.metric_type)
+
+        got = {}
+        for key, lo, hi in (("job-0", 0, 20), ("job-1", 0, 20), ("job-0", 20, 50), ("job-2", 0, 50), ("job-1", 20, 50)):
+            b = window(key, lo, hi)
+            r = cache.score(key, history(key), b)
+            got.setdefault(key, []).append(r.series()["n_anom"][:, 4].copy())
+            r.free()
+            b.free()
+        # job-0 hit its model on the second cycle; job-2 evicted job-1 (least recently used), so job-1 was fitted twice
+        assert fits == ["job-0", "job-1", "job-2", "job-1"]
+        assert (cache.hits, cache.misses, cache.evictions, len(cache)) == (1, 4, 2, 2)
+        assert "job-1" in cache and "job-2" in cache and "job-0" not in cache
+        # two cached cycles of job-0 = one oracle pass over history + both windows
+        full, _ = jobs["job-0"]
+        ref = oracle.score(full, p)[0]
+        fitted = ((ref["status"] >> (abi.S_ALG_SHIFT + 4)) & 1) == 1
+        assert fitted.all() and np.array_equal((got["job-0"][0] + got["job-0"][1])[fitted], ref["n_anom"][fitted, 4])
+        cache.clear()
+        assert len(cache) == 0
