@@ -317,6 +317,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
                                                               const unsigned long long *__restrict__ emit_off,
                                                               uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val) {
   constexpr bool BANDS = MODE == 1, EMIT = MODE == 2;
+  // chunk bodies: eight groups of four samples.  Kernels that carry the rolling band keep them rolled (its
+  // per-point code times 32 samples times five variants was 11 k instructions and waited on instruction fetch);
+  // the others fit the instruction cache unrolled and are 3-8 % faster that way
+  constexpr int kChunkUnroll = (ALGS & FM_ALG_MA_ROLLING) ? 1 : 8;
   constexpr int kSlot = (ALGS & FM_ALG_MA_ALL) ? 0 : (ALGS & FM_ALG_EWMA) ? 1 : (ALGS & FM_ALG_DES) ? 2 : 3;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
@@ -442,7 +446,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     if (roll_deep && __all_sync(0xffffffffu, (cls_src && cs >= a0 + 32u) || dontcare)) {
       // rolled over the eight groups of four samples: the unrolled chunk bodies of all variants together
       // were 11 k instructions in the four-scorer kernel and it waited on instruction fetch
-#pragma unroll 1
+#pragma unroll kChunkUnroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t i0 = v4 * 4;
@@ -454,7 +458,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       }
     } else if (__all_sync(0xffffffffu, cls_src || dontcare)) {
       // whole chunk inside the model window for every lane: no range checks
-#pragma unroll 1
+#pragma unroll kChunkUnroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t q = cs + v4 * 4 - a0;
@@ -470,7 +474,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
       // so the band arrays are written in full 128 B lines instead of 4 B at a 5.7 KB stride.
       float *uprow = s_ring + (ch % kSlots) * (32 * kRowWords) + lane * kRowWords;
       float *lorow = s_lo + lane * kRowWords;
-#pragma unroll 1
+#pragma unroll kChunkUnroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(uprow + v4 * 4);
         const uint32_t j = cs + v4 * 4 - c0;
@@ -497,7 +501,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     } else if (MODE == 0 && roll_deep && __all_sync(0xffffffffu, (cls_cur && cs >= c0 + 32u) || dontcare)) {
       uint32_t mask[4] = {0u, 0u, 0u, 0u};
       const uint32_t j0 = cs - c0;
-#pragma unroll 1
+#pragma unroll kChunkUnroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t i0 = v4 * 4;
@@ -518,7 +522,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
     } else if (MODE == 0 && __all_sync(0xffffffffu, cls_cur || dontcare)) {
       uint32_t mask[4] = {0u, 0u, 0u, 0u};
       const uint32_t j0 = cs - c0;
-#pragma unroll 1
+#pragma unroll kChunkUnroll
       for (int v4 = 0; v4 < 8; ++v4) {
         const float4 x = *reinterpret_cast<const float4 *>(row + v4 * 4);
         const uint32_t i0 = v4 * 4;
