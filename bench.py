@@ -465,10 +465,13 @@ def run_ours(args):
                              if cpu_rate is not None else None),
             "e2e": {"value": n * world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps},
-            # per step: k_rank (Wilcoxon), k_rank (MWU/Kruskal), k_rank_finalize, k_band, k_verdict_reduce,
-            # k_verdict_finalize; the e2e call runs the first five once per ~256 MiB upload chunk
-            "gpu_launches": 6 * args.steps + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 3 * 8 * 2 + 1
-            + (10 * 3 + 5 * 4 + 2 + 220 * 5 if other else 0),  # cfg2, cfg4, their generators, cfg0's 220 calls
+            # inside the timed region, per step: k_wilcoxon, k_mw, k_rank_finalize, k_band, k_verdict_reduce,
+            # k_verdict_finalize (+ NCCL's own all-reduce kernel at N > 1, not counted: it is not ours)
+            "gpu_launches": 6 * args.steps,
+            # the untimed legs: the parity pass, the per-scorer passes, the e2e calls (the five scoring kernels once per
+            # ~256 MiB upload chunk + one finalize), cfg2 / cfg4 / cfg0 / ingest, their generators
+            "gpu_launches_other_legs": 6 + 5 * 8 * 2 + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 1
+            + (10 * 3 + 5 * 4 + 2 + 220 * 5 + 4 * 5 if other else 0),
             "clocks": clocks,
             "verdict_summary": {"services": int(verdicts.size), "unhealth": int((verdicts["verdict"] == abi.V_UNHEALTH).sum()),
                                 "unknown": int((verdicts["verdict"] == abi.V_UNKNOWN).sum()),
