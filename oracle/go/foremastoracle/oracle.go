@@ -83,6 +83,9 @@ const (
 const NoneIdx uint32 = 0xFFFFFFFF
 
 // MetricRule is one row of the threshold table, foremast-brain.yaml:26-73.
+// RankMaxSegment is FM_RANK_MAX_SEGMENT of include/foremast_gpu.h (DECISIONS D17).
+const RankMaxSegment = 2048
+
 type MetricRule struct {
 	Threshold     float64
 	MinLowerBound float64
@@ -323,9 +326,11 @@ func ScoreUnit(p *Params, hist, base, cur []float32, mt uint8, bandUp, bandLo []
 	if nc < m {
 		m = nc
 	}
-	runMW := wantMW && nb >= p.MinMannWhite && nc >= p.MinMannWhite && m > 0
-	runW := wantW && m >= p.MinWilcoxon && m > 0
-	runK := wantK && nb >= p.MinKruskal && nc >= p.MinKruskal && m > 0
+	// D17: rank tests look at segments of at most RankMaxSegment samples (Wilcoxon: pairs)
+	shortEnough := nb <= RankMaxSegment && nc <= RankMaxSegment
+	runMW := wantMW && nb >= p.MinMannWhite && nc >= p.MinMannWhite && m > 0 && shortEnough
+	runW := wantW && m >= p.MinWilcoxon && m > 0 && m <= RankMaxSegment
+	runK := wantK && nb >= p.MinKruskal && nc >= p.MinKruskal && m > 0 && shortEnough
 	nRun, nRej := 0, 0
 	if runMW || runK {
 		keys := make([]uint64, 0, nb+nc)
