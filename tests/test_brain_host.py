@@ -205,3 +205,42 @@ def test_metrics_endpoint_serves_bands_and_hpa_score():
         assert all(re.match(r"^(#|foremastbrain[:\w]*\{)", ln) for ln in page.strip().split("\n"))  # adapter: ^foremastbrain.*
     finally:
         srv.close()
+
+
+def test_regridding_fuzz_against_python():
+    """Random scrape gaps, several series per response, integer and fractional timestamps: the scanner's grid
+    placement (NaN holes, forward fill) against a straightforward Python re-grid of the same points."""
+    rng = np.random.default_rng(17)
+    for trial in range(40):
+        step = float(rng.choice([15, 30, 60, 300]))
+        t0 = 1550000000 + (0.25 if trial % 3 == 0 else 0.0)
+        result, want_nan, want_fill, missing = [], [], [], []
+        for s in range(int(rng.integers(1, 5))):
+            n = int(rng.integers(2, 120))
+            keep = rng.random(n) > rng.choice([0.0, 0.1, 0.4])
+            keep[0] = keep[-1] = True
+            if keep.sum() < 2:
+                keep[1] = True
+            # make sure two neighbours survive somewhere, so that the smallest gap IS the step (no hint given)
+            j = int(rng.integers(0, n - 1))
+            keep[j] = keep[j + 1] = True
+            vals = np.round(rng.normal(10, 3, n), 3).astype(np.float32)
+            result.append({"metric": {"pod": f"p{s}"}, "values": [[t0 + step * i, repr(float(vals[i]))] for i in range(n) if keep[i]]})
+            g = np.where(keep, vals, np.nan).astype(np.float32)
+            f = g.copy()
+            for i in range(1, n):
+                if np.isnan(f[i]):
+                    f[i] = f[i - 1]
+            want_nan.append(g)
+            want_fill.append(f)
+            missing.append(int((~keep).sum()))
+        body = json.dumps({"status": "success", "data": {"resultType": "matrix", "result": result}}).encode()
+        for flags, want in ((abi.PROM_GRID, want_nan), (abi.PROM_GRID | abi.PROM_FILL, want_fill)):
+            for hint in (0.0, step):
+                series, values = brain.parse_matrix_series(body, flags, hint)
+                assert len(series) == len(want)
+                for rec, w, miss in zip(series, want, missing):
+                    got = values[int(rec["first_value"]):int(rec["first_value"]) + int(rec["n_values"])]
+                    assert int(rec["reserved"]) == miss and float(rec["step"]) == step
+                    assert got.shape == w.shape and np.array_equal(np.isnan(got), np.isnan(w))
+                    assert np.array_equal(got[~np.isnan(got)], w[~np.isnan(w)])
