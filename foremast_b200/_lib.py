@@ -49,6 +49,7 @@ SYMBOLS = {
     "fm_score_host": (C.c_int, [_P, C.POINTER(abi.Csr), C.POINTER(abi.Params), C.c_uint32, _P]),
     "fm_result_sync": (C.c_int, [_P]),
     "fm_result_verdicts": (C.c_int, [_P, _P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "fm_result_verdicts_range": (C.c_int, [_P, C.c_uint64, C.c_uint64, _P]),
     "fm_result_series": (C.c_int, [_P, C.c_uint64, C.c_uint64, _P]),
     "fm_result_bands": (C.c_int, [_P, C.c_uint64, _P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "fm_result_anomalies_build": (C.c_int, [_P, C.c_uint32, C.POINTER(C.c_uint64)]),

@@ -297,6 +297,16 @@ class Result:
         self.ctx._check(self.ctx._L.fm_result_verdicts(self._h, out.ctypes.data, ns, C.byref(n)))
         return out
 
+    def verdicts_range(self, first, count, out=None):
+        """Verdicts of services [first, first + count) only (fm_result_verdicts_range): what a rank of a sharded
+        sweep downloads after merge() -- its own services."""
+        if out is None:
+            out = np.zeros(count, dtype=abi.VERDICT)
+        assert out.dtype == abi.VERDICT and out.size >= count and out.flags.c_contiguous
+        out = out[:count]
+        self.ctx._check(self.ctx._L.fm_result_verdicts_range(self._h, first, count, out.ctypes.data if count else None))
+        return out
+
     def series(self, first=0, count=None):
         n = self.batch.info()["n_units"]
         count = n - first if count is None else count

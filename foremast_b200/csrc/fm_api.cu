@@ -896,9 +896,27 @@ int fm_result_verdicts(fm_result *r, fm_verdict *out, uint64_t cap, uint64_t *n)
   if (cap < r->n_services) return set_err(ctx, FM_E_RANGE, "verdict buffer too small");
   if (r->n_services == 0) return FM_OK;
   // finalised at read time so that a cross-GPU merge of the counters can happen in between
-  fm_launch_verdict_finalize(r->n_services, r->d_counts, r->d_worst, r->d_verdicts, ctx->stream);
+  fm_launch_verdict_finalize(r->n_services, r->d_counts, r->d_worst, r->d_verdicts, 0u, ctx->stream);
   FM_CUDA(ctx, cudaGetLastError());
   FM_CUDA(ctx, cudaMemcpyAsync(out, r->d_verdicts, r->n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, ctx->stream));
+  FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FM_OK;
+}
+
+// A slice of the verdict vector: after a cross-GPU merge every rank holds all counters, but a rank usually
+// reports only the services of its own shard.
+int fm_result_verdicts_range(fm_result *r, uint64_t first_service, uint64_t count, fm_verdict *out) {
+  if (!r || (!out && count)) return FM_E_INVALID;
+  fm_ctx *ctx = r->ctx;
+  if (first_service > r->n_services || count > r->n_services - first_service)
+    return set_err(ctx, FM_E_RANGE, "service range outside the result");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  FM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (count == 0) return FM_OK;
+  fm_launch_verdict_finalize((uint32_t)count, r->d_counts + 4 * first_service, r->d_worst + first_service,
+                             r->d_verdicts + first_service, (uint32_t)first_service, ctx->stream);
+  FM_CUDA(ctx, cudaGetLastError());
+  FM_CUDA(ctx, cudaMemcpyAsync(out, r->d_verdicts + first_service, count * sizeof(fm_verdict), cudaMemcpyDeviceToHost, ctx->stream));
   FM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return FM_OK;
 }
@@ -1145,7 +1163,7 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
     rc = launch_range(ctx, &sr, &tb, p, 0, n, false);
     if (rc) { cudaStreamSynchronize(st); return rc; }
     if (n_services) {
-      fm_launch_verdict_finalize(n_services, sr.d_counts, sr.d_worst, sr.d_verdicts, st);
+      fm_launch_verdict_finalize(n_services, sr.d_counts, sr.d_worst, sr.d_verdicts, 0u, st);
       FM_CUDA(ctx, cudaGetLastError());
       FM_CUDA(ctx, cudaMemcpyAsync(hs + kOffVerdicts, sr.d_verdicts, n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, st));
     }
@@ -1217,7 +1235,7 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
     if (rc) { cleanup(); return rc; }
     i0 = i1;
   }
-  fm_launch_verdict_finalize(n_services, r->d_counts, r->d_worst, r->d_verdicts, st);
+  fm_launch_verdict_finalize(n_services, r->d_counts, r->d_worst, r->d_verdicts, 0u, st);
   FM_H(cudaGetLastError());
   if (n_services)
     FM_H(cudaMemcpyAsync(verdicts, r->d_verdicts, n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, st));

@@ -41,13 +41,14 @@ __global__ void __launch_bounds__(256) k_verdict_reduce(DevBatch b, const uint32
   }
 }
 
+// counts / worst / out point at the first service of the range, whose id is `first_service`
 __global__ void __launch_bounds__(256) k_verdict_finalize(uint32_t n_services, const uint32_t *__restrict__ counts,
                                                           const unsigned long long *__restrict__ worst,
-                                                          fm_verdict *__restrict__ out) {
+                                                          fm_verdict *__restrict__ out, uint32_t first_service) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_services) return;
   fm_verdict v;
-  v.service_id = s;
+  v.service_id = first_service + s;
   v.n_units = counts[4ull * s + 0];
   v.n_unknown = counts[4ull * s + 1];
   v.n_anom_units = counts[4ull * s + 2];
@@ -76,7 +77,7 @@ void fm_launch_verdict_reduce(const DevBatch &b, const uint32_t *unit_status, co
 }
 
 void fm_launch_verdict_finalize(uint32_t n_services, const uint32_t *counts, const unsigned long long *worst,
-                                fm_verdict *out, cudaStream_t st) {
+                                fm_verdict *out, uint32_t first_service, cudaStream_t st) {
   if (n_services == 0) return;
-  k_verdict_finalize<<<(n_services + 255) / 256, 256, 0, st>>>(n_services, counts, worst, out);
+  k_verdict_finalize<<<(n_services + 255) / 256, 256, 0, st>>>(n_services, counts, worst, out, first_service);
 }

@@ -316,6 +316,9 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *host_csr, const fm_params *p,
 int fm_result_sync(fm_result *r);
 /* status `completed_health|completed_unhealth|completed_unknown` per service (converter.go:16-21). */
 int fm_result_verdicts(fm_result *r, fm_verdict *out, uint64_t cap, uint64_t *n);
+/* The verdicts of services [first_service, first_service + count) only: after fm_result_merge every rank
+ * holds all counters, and a rank of a sharded sweep usually writes back only the documents of its own shard. */
+int fm_result_verdicts_range(fm_result *r, uint64_t first_service, uint64_t count, fm_verdict *out);
 int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_series_score *out);
 /* upper/lower band of the current segment of one unit, for the foremastbrain:*_upper/_lower
  * gauges (foremast-dashboard/src/config/metrics.js:20-31).  Needs params.band_algorithm. */

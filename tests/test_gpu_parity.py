@@ -546,6 +546,11 @@ def test_library_comm_single_rank_merge_is_identity(ctx, oracle):
         host = b.download()
         ref, _, _ = oracle.score(host, p)
         assert got.tobytes() == oracle.verdicts(host, ref, b.info()["n_services"]).tobytes()
+        ns = b.info()["n_services"]
+        assert res.verdicts_range(3, ns - 5).tobytes() == got[3:ns - 2].tobytes()   # a slice = the same records, ids kept
+        assert res.verdicts_range(ns, 0).size == 0
+        with pytest.raises(Exception):
+            res.verdicts_range(ns - 1, 2)
         res.free()
         b.free()
     finally:
@@ -582,6 +587,8 @@ def test_library_comm_two_gpus_merge_matches_oracle_fold(oracle):
             res = c.score(b, p)
             res.merge()
             out[rank] = res.verdicts().copy()
+            s_lo, s_hi = -(-lo // ups), -(-hi // ups)
+            assert res.verdicts_range(s_lo, s_hi - s_lo).tobytes() == out[rank][s_lo:s_hi].tobytes()
             res.free()
             b.free()
             c.close()
