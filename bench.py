@@ -373,6 +373,24 @@ def run_ours(args):
         v2 = ctx.score_host(host_p, p, total_services, out=vout)
     barrier()
     e2e_s = (time.perf_counter() - t1) / e2e_steps
+    # the ceiling of that number: the same pinned bytes, bare cudaMemcpyAsync host -> device, all ranks at once
+    copy_s = None
+    try:
+        import ctypes as C
+        rt = C.CDLL("libcudart.so.12")
+        rt.cudaMemcpyAsync.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        dst = torch.empty(pv.nbytes, dtype=torch.uint8, device="cuda")
+        for i in range(4):
+            if i == 1:
+                barrier()
+                t2 = time.perf_counter()
+            assert rt.cudaMemcpyAsync(dst.data_ptr(), pin_ptr, pv.nbytes, 1, None) == 0
+            torch.cuda.synchronize()
+        barrier()
+        copy_s = (time.perf_counter() - t2) / 3
+        del dst
+    except Exception as e:  # the ceiling is an annotation, not part of the result
+        sys.stderr.write(f"bare-copy ceiling not measured: {e}\n")
     clocks = sampler.stop() if rank == 0 else None
     # the services that lie wholly inside this rank's shard: there the merged verdicts, the one-shot call's
     # (un-merged) verdicts and the oracle fold of the shard must all be the same bytes
@@ -404,13 +422,13 @@ def run_ours(args):
         verdict_equal, services_checked = True, 0
     del ref, gpu_series
 
-    t = torch.tensor([dev_ms, wall_ms, e2e_s * 1e3, worst_rel, float(not verdict_equal), float(not e2e_equal)],
-                     dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, wall_ms, e2e_s * 1e3, worst_rel, float(not verdict_equal), float(not e2e_equal),
+                      (copy_s or 0.0) * 1e3], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([int_mis, n_par, services_checked], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    dev_ms, wall_ms, e2e_ms, worst_rel, verdict_bad, e2e_bad = (float(x) for x in t.tolist())
+    dev_ms, wall_ms, e2e_ms, worst_rel, verdict_bad, e2e_bad, copy_ms = (float(x) for x in t.tolist())
     int_mis, units_checked, services_checked = (int(x) for x in cnt.tolist())
     parity = {"units_checked": units_checked, "int_mismatches": int_mis, "max_float_rel_err": worst_rel,
               "float_tolerance": REL_TOL, "verdict_bytes_equal": verdict_bad == 0.0, "services_checked": services_checked,
@@ -472,7 +490,11 @@ def run_ours(args):
                               "sample": f"first {sample} units of rank 0's batch (the parity pass), one pass, {cpu_s:.2f} s"}
                              if cpu_rate is not None else None),
             "e2e": {"value": n * world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps},
+                    "d2h_bytes_per_step": int(total_services * 32), "ms_per_step": e2e_ms, "steps": e2e_steps,
+                    # bare concurrent pinned host -> device copy of the same sample bytes on all N ranks: what the link
+                    # and the host memory system allow; the call's own time as a fraction of it
+                    "bare_h2d_copy_ms": copy_ms or None,
+                    "frac_of_bare_copy": (copy_ms / e2e_ms) if copy_ms else None},
             # inside the timed region, per step: k_wilcoxon, k_mw, k_rank_finalize, k_band, k_verdict_reduce,
             # k_verdict_finalize (+ NCCL's own all-reduce kernel at N > 1, not counted: it is not ours)
             "gpu_launches": 6 * args.steps,
