@@ -120,6 +120,9 @@ int set_err(fm_ctx *ctx, int code, const std::string &msg) {
   return code;
 }
 
+// a NULL / malformed argument: the stale text of an earlier failure must not be what fm_last_error shows next
+int bad_arg(const fm_ctx *ctx, const char *fn) { return set_err(const_cast<fm_ctx *>(ctx), FM_E_INVALID, std::string(fn) + ": NULL or inconsistent argument"); }
+
 #define FM_CUDA(ctx, expr)                                                                      \
   do {                                                                                          \
     cudaError_t _e = (expr);                                                                    \
@@ -300,7 +303,7 @@ const char *fm_last_error(const fm_ctx *ctx) {
 }
 
 int fm_last_error_copy(const fm_ctx *ctx, char *buf, uint32_t cap) {
-  if (!ctx || !buf || cap == 0) return FM_E_INVALID;
+  if (!ctx || !buf || cap == 0) return bad_arg(ctx, __func__);
   fm_ctx *c = const_cast<fm_ctx *>(ctx);
   std::lock_guard<std::mutex> g(c->err_mu);
   snprintf(buf, cap, "%s", c->last_error.c_str());
@@ -383,7 +386,7 @@ void fm_shutdown(fm_ctx *ctx) {
 }
 
 int fm_device_info(const fm_ctx *ctx, int32_t *sm_count, uint64_t *hbm_bytes, char *name, uint32_t name_cap) {
-  if (!ctx) return FM_E_INVALID;
+  if (!ctx) return bad_arg(ctx, __func__);
   if (sm_count) *sm_count = ctx->sm_count;
   if (hbm_bytes) *hbm_bytes = ctx->hbm_bytes;
   if (name && name_cap) snprintf(name, name_cap, "%s", ctx->name);
@@ -391,7 +394,7 @@ int fm_device_info(const fm_ctx *ctx, int32_t *sm_count, uint64_t *hbm_bytes, ch
 }
 
 int fm_timer_start(fm_ctx *ctx) {
-  if (!ctx) return FM_E_INVALID;
+  if (!ctx) return bad_arg(ctx, __func__);
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   for (auto &e : ctx->timer)
@@ -401,7 +404,7 @@ int fm_timer_start(fm_ctx *ctx) {
 }
 
 int fm_timer_stop(fm_ctx *ctx, float *ms) {
-  if (!ctx || !ms || !ctx->timer[0]) return FM_E_INVALID;
+  if (!ctx || !ms || !ctx->timer[0]) return bad_arg(ctx, __func__);
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   FM_CUDA(ctx, cudaEventRecord(ctx->timer[1], ctx->stream));
@@ -411,7 +414,7 @@ int fm_timer_stop(fm_ctx *ctx, float *ms) {
 }
 
 int fm_host_alloc(fm_ctx *ctx, uint64_t bytes, void **out) {
-  if (!ctx || !out) return FM_E_INVALID;
+  if (!ctx || !out) return bad_arg(ctx, __func__);
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   FM_CUDA(ctx, cudaMallocHost(out, bytes ? bytes : 1));
@@ -428,7 +431,7 @@ void fm_host_free(fm_ctx *ctx, void *p) {
 // ------------------------------------------------------------------ ingest
 
 int fm_batch_begin(fm_ctx *ctx, uint64_t n_units_hint, uint64_t n_points_hint, fm_batch **out) {
-  if (!ctx || !out) return FM_E_INVALID;
+  if (!ctx || !out) return bad_arg(ctx, __func__);
   fm_batch *b = new (std::nothrow) fm_batch;
   if (!b) return FM_E_NOMEM;
   b->ctx = ctx;
@@ -448,7 +451,7 @@ int fm_batch_begin(fm_ctx *ctx, uint64_t n_units_hint, uint64_t n_points_hint, f
 
 int fm_batch_add_series(fm_batch *b, const fm_series_meta *meta, const float *hist, uint32_t n_hist,
                         const float *base, uint32_t n_base, const float *cur, uint32_t n_cur) {
-  if (!b || !meta || (n_hist && !hist) || (n_base && !base) || (n_cur && !cur)) return FM_E_INVALID;
+  if (!b || !meta || (n_hist && !hist) || (n_base && !base) || (n_cur && !cur)) return bad_arg(b ? b->ctx : nullptr, __func__);
   if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
   try {
     b->h_offsets.push_back((int64_t)b->h_values.size());
@@ -477,7 +480,7 @@ int fm_batch_add_series(fm_batch *b, const fm_series_meta *meta, const float *hi
 
 int fm_batch_reserve_units(fm_batch *b, uint64_t n, const uint32_t *seg_lens, const uint32_t *service_id,
                            const uint8_t *metric_type, float **values_out, uint64_t *rel_off) {
-  if (!b || (n && (!seg_lens || !values_out || !rel_off))) return FM_E_INVALID;
+  if (!b || (n && (!seg_lens || !values_out || !rel_off))) return bad_arg(b ? b->ctx : nullptr, __func__);
   if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
   try {
     const uint64_t start = b->h_values.size();
@@ -501,7 +504,7 @@ int fm_batch_reserve_units(fm_batch *b, uint64_t n, const uint32_t *seg_lens, co
 extern "C" {
 
 int fm_batch_seal(fm_batch *b) {
-  if (!b) return FM_E_INVALID;
+  if (!b) return bad_arg(b ? b->ctx : nullptr, __func__);
   if (b->sealed) return set_err(b->ctx, FM_E_STATE, "batch already sealed");
   fm_ctx *ctx = b->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
@@ -529,7 +532,7 @@ int fm_batch_seal(fm_batch *b) {
 }
 
 int fm_batch_from_csr(fm_ctx *ctx, const fm_csr *h, fm_batch **out) {
-  if (!ctx || !h || !out || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return FM_E_INVALID;
+  if (!ctx || !h || !out || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return bad_arg(ctx, __func__);
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   fm_batch *b = new (std::nothrow) fm_batch;
@@ -569,7 +572,7 @@ int fm_batch_from_csr(fm_ctx *ctx, const fm_csr *h, fm_batch **out) {
 }
 
 int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
-  if (!ctx || !d || !out || !d->values || !d->offsets || !d->seg_lens || !d->service_id || !d->metric_type) return FM_E_INVALID;
+  if (!ctx || !d || !out || !d->values || !d->offsets || !d->seg_lens || !d->service_id || !d->metric_type) return bad_arg(ctx, __func__);
   if (reinterpret_cast<uintptr_t>(d->values) & 15) return set_err(ctx, FM_E_ALIGN, "values pointer is not 16-byte aligned");
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -611,7 +614,7 @@ int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
 }
 
 int fm_batch_synth(fm_ctx *ctx, const fm_synth_config *cfg, fm_batch **out) {
-  if (!ctx || !cfg || !out || cfg->n_metric_types == 0 || cfg->n_metric_types > 8 || cfg->units_per_service == 0) return FM_E_INVALID;
+  if (!ctx || !cfg || !out || cfg->n_metric_types == 0 || cfg->n_metric_types > 8 || cfg->units_per_service == 0) return bad_arg(ctx, __func__);
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   fm_batch *b = new (std::nothrow) fm_batch;
@@ -637,7 +640,7 @@ int fm_batch_synth(fm_ctx *ctx, const fm_synth_config *cfg, fm_batch **out) {
 }
 
 int fm_batch_set_shard(fm_batch *b, uint64_t first_unit, uint32_t n_services) {
-  if (!b) return FM_E_INVALID;
+  if (!b) return bad_arg(b ? b->ctx : nullptr, __func__);
   if (n_services < b->n_services) return set_err(b->ctx, FM_E_RANGE, "n_services smaller than the largest service id + 1");
   b->first_unit = first_unit;
   b->n_services = n_services;
@@ -645,7 +648,7 @@ int fm_batch_set_shard(fm_batch *b, uint64_t first_unit, uint32_t n_services) {
 }
 
 int fm_batch_info(const fm_batch *b, uint64_t *n_units, uint64_t *n_values, uint32_t *n_services) {
-  if (!b) return FM_E_INVALID;
+  if (!b) return bad_arg(b ? b->ctx : nullptr, __func__);
   if (n_units) *n_units = b->n_units;
   if (n_values) *n_values = b->n_values;
   if (n_services) *n_services = b->n_services;
@@ -653,7 +656,7 @@ int fm_batch_info(const fm_batch *b, uint64_t *n_units, uint64_t *n_values, uint
 }
 
 int fm_batch_download(const fm_batch *b, float *values, int64_t *offsets, uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type) {
-  if (!b || !b->sealed) return FM_E_INVALID;
+  if (!b || !b->sealed) return bad_arg(b ? b->ctx : nullptr, __func__);
   fm_ctx *ctx = b->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -792,7 +795,7 @@ static int score_locked(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
 }
 
 int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out) {
-  if (!ctx || !b || !p || !out) return FM_E_INVALID;
+  if (!ctx || !b || !p || !out) return bad_arg(ctx, __func__);
   if (!b->sealed) return set_err(ctx, FM_E_STATE, "batch is not sealed");
   if (b->ctx != ctx) return set_err(ctx, FM_E_INVALID, "batch belongs to another context");
   std::lock_guard<std::mutex> g(ctx->mu);
@@ -803,7 +806,7 @@ int fm_score(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_result **out
 // ---- continuous-mode model cache (Holt-Winters state kept in HBM between cycles)
 
 int fm_model_fit(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_model **out) {
-  if (!ctx || !b || !p || !out) return FM_E_INVALID;
+  if (!ctx || !b || !p || !out) return bad_arg(ctx, __func__);
   if (!b->sealed || b->ctx != ctx) return set_err(ctx, FM_E_STATE, "batch is not a sealed batch of this context");
   if (p->period < 32 || p->period > 2048) return set_err(ctx, FM_E_UNSUPPORTED, "Holt-Winters period must be between 32 and 2048 samples");
   std::lock_guard<std::mutex> g(ctx->mu);
@@ -834,7 +837,7 @@ int fm_model_fit(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_model **
 }
 
 int fm_model_score(fm_ctx *ctx, fm_model *m, const fm_batch *b, fm_result **out) {
-  if (!ctx || !m || !b || !out) return FM_E_INVALID;
+  if (!ctx || !m || !b || !out) return bad_arg(ctx, __func__);
   if (!b->sealed || b->ctx != ctx || m->ctx != ctx) return set_err(ctx, FM_E_STATE, "batch / model do not belong to this context");
   if (b->n_units != m->n_units) return set_err(ctx, FM_E_INVALID, "the current batch must hold the same units, in the same order, as the fitted one");
   std::lock_guard<std::mutex> g(ctx->mu);
@@ -879,7 +882,7 @@ void fm_model_free(fm_model *m) {
 }
 
 int fm_result_sync(fm_result *r) {
-  if (!r) return FM_E_INVALID;
+  if (!r) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -888,7 +891,7 @@ int fm_result_sync(fm_result *r) {
 }
 
 int fm_result_verdicts(fm_result *r, fm_verdict *out, uint64_t cap, uint64_t *n) {
-  if (!r || !out) return FM_E_INVALID;
+  if (!r || !out) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -906,7 +909,7 @@ int fm_result_verdicts(fm_result *r, fm_verdict *out, uint64_t cap, uint64_t *n)
 // A slice of the verdict vector: after a cross-GPU merge every rank holds all counters, but a rank usually
 // reports only the services of its own shard.
 int fm_result_verdicts_range(fm_result *r, uint64_t first_service, uint64_t count, fm_verdict *out) {
-  if (!r || (!out && count)) return FM_E_INVALID;
+  if (!r || (!out && count)) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   if (first_service > r->n_services || count > r->n_services - first_service)
     return set_err(ctx, FM_E_RANGE, "service range outside the result");
@@ -922,7 +925,7 @@ int fm_result_verdicts_range(fm_result *r, uint64_t first_service, uint64_t coun
 }
 
 int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_series_score *out) {
-  if (!r || (!out && count)) return FM_E_INVALID;
+  if (!r || (!out && count)) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   if (first_unit > r->n_units || count > r->n_units - first_unit) return set_err(ctx, FM_E_RANGE, "unit range outside the batch");
   std::lock_guard<std::mutex> g(ctx->mu);
@@ -934,7 +937,7 @@ int fm_result_series(fm_result *r, uint64_t first_unit, uint64_t count, fm_serie
 }
 
 int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uint32_t cap, uint32_t *n) {
-  if (!r || !upper || !lower) return FM_E_INVALID;
+  if (!r || !upper || !lower) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   if (!r->d_band_up) return set_err(ctx, FM_E_STATE, "bands were not requested (params.band_algorithm == 0)");
   if (unit >= r->n_units) return set_err(ctx, FM_E_RANGE, "unit outside the batch");
@@ -959,7 +962,7 @@ int fm_result_bands(fm_result *r, uint64_t unit, float *upper, float *lower, uin
 // ---- compact anomaly list (a10)
 
 int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_points) {
-  if (!r) return FM_E_INVALID;
+  if (!r) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   int a = -1;
   for (int i = 0; i < FM_N_ALG; ++i)
@@ -1001,7 +1004,7 @@ int fm_result_anomalies_build(fm_result *r, uint32_t algorithm, uint64_t *n_poin
 }
 
 int fm_result_anomalies_unit(fm_result *r, uint64_t unit, uint32_t *cur_idx, float *values, uint32_t cap, uint32_t *n) {
-  if (!r || !n) return FM_E_INVALID;
+  if (!r || !n) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   if (!r->d_anom_off) return set_err(ctx, FM_E_STATE, "call fm_result_anomalies_build first");
   if (unit >= r->n_units) return set_err(ctx, FM_E_RANGE, "unit outside the batch");
@@ -1020,7 +1023,7 @@ int fm_result_anomalies_unit(fm_result *r, uint64_t unit, uint32_t *cur_idx, flo
 }
 
 int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, float *values, uint64_t cap) {
-  if (!r) return FM_E_INVALID;
+  if (!r) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   if (!r->d_anom_off) return set_err(ctx, FM_E_STATE, "call fm_result_anomalies_build first");
   if (cap < r->anom_total) return set_err(ctx, FM_E_RANGE, "anomaly buffer too small");
@@ -1035,7 +1038,7 @@ int fm_result_anomalies_all(fm_result *r, uint64_t *offsets, uint32_t *cur_idx, 
 }
 
 int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst, uint32_t *n_services) {
-  if (!r) return FM_E_INVALID;
+  if (!r) return bad_arg(r ? r->ctx : nullptr, __func__);
   if (counts) *counts = r->d_counts;
   if (worst) *worst = reinterpret_cast<uint64_t *>(r->d_worst);
   if (n_services) *n_services = r->n_services;
@@ -1045,7 +1048,7 @@ int fm_result_service_buffers(fm_result *r, uint32_t **counts, uint64_t **worst,
 // Cross-GPU merge of the per-service counters, in place, ordered on the context's stream between the
 // scoring kernels and the finalize pass of fm_result_verdicts: no host synchronisation in between.
 int fm_result_merge(fm_result *r) {
-  if (!r) return FM_E_INVALID;
+  if (!r) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1053,7 +1056,7 @@ int fm_result_merge(fm_result *r) {
 }
 
 int fm_result_timings(fm_result *r, float *ms, uint32_t cap) {
-  if (!r || !ms || cap < 5) return FM_E_INVALID;
+  if (!r || !ms || cap < 5) return bad_arg(r ? r->ctx : nullptr, __func__);
   fm_ctx *ctx = r->ctx;
   std::lock_guard<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1073,7 +1076,7 @@ void fm_result_free(fm_result *r) {
 // chunked on a second stream and each chunk is scored as soon as it has landed, so PCIe and the
 // kernels overlap; with pinned input (fm_host_alloc) the call runs at PCIe speed.
 int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_services, fm_verdict *verdicts) {
-  if (!ctx || !h || !p || !verdicts || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return FM_E_INVALID;
+  if (!ctx || !h || !p || !verdicts || (h->n_units && (!h->values || !h->offsets || !h->seg_lens))) return bad_arg(ctx, __func__);
   std::unique_lock<std::mutex> g(ctx->mu);
   FM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = validate_params(ctx, p);
