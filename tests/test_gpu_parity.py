@@ -603,3 +603,40 @@ def test_library_comm_two_gpus_merge_matches_oracle_fold(oracle):
     assert not errs, errs
     for r in range(world):
         assert out[r] is not None and out[r].tobytes() == want.tobytes()
+
+
+def test_mann_whitney_search_kernel_extremes(ctx, oracle):
+    """k_mw sorts only the baseline and finds every current sample by a lower bound, with equal values among
+    the current samples resolved by the duplicate rounds: shapes and value patterns at the edges of that scheme --
+    very unequal lengths, a full tile, every current sample equal, every current sample equal to a long run of
+    the baseline, current samples all below / all above / all inside one gap, negative values and zeros of both
+    signs, and keys that collide in the id table by construction (many distinct values)."""
+    rng = np.random.default_rng(99)
+    z = rng.normal(0, 1, 5000).astype(np.float32)
+    grid = (np.arange(2048) * 0.5 - 300).astype(np.float32)
+    units = [
+        (z[:20], z[:2048], z[2048:2049]),                                   # 2048 vs 1
+        (z[:20], z[:1], z[1:2049]),                                         # 1 vs 2048
+        (z[:20], grid, grid[::-1].copy()),                                  # full tiles, every value met exactly once
+        (z[:20], grid, np.full(2048, grid[77], np.float32)),                # all current samples equal one baseline value
+        (z[:20], np.full(1000, 3.25, np.float32), np.full(900, 3.25, np.float32)),   # one pooled tie group
+        (z[:20], np.repeat(grid[:64], 16), np.repeat(grid[32:96], 9)),      # long runs on both sides, half of them shared
+        (z[:20], z[:700], z[700:1400] - 100),                               # all current below the baseline
+        (z[:20], z[:700], z[700:1400] + 100),                               # all above
+        (z[:20], np.concatenate([z[:350] - 50, z[350:700] + 50]), rng.integers(0, 3, 700).astype(np.float32) * 0.25),  # one gap, heavy ties
+        (z[:20], np.array([-0.0, 0.0, -1.0, 1.0] * 100, np.float32), np.array([0.0, -0.0, 0.0, 2.0, -2.0] * 90, np.float32)),
+        (z[:20], z[:720], np.arange(720, dtype=np.float32) * 1e-3),         # 720 distinct keys: slot collisions, no ties
+        (z[:20], np.arange(720, dtype=np.float32), np.arange(720, dtype=np.float32)[::-1].copy() + 0.5),  # interleaved, no ties
+        (z[:20], z[:5], z[5:10]),                                           # min_kruskal only
+    ]
+    b = ctx.batch_from_units(units, service_id=[i // 4 for i in range(len(units))], metric_type=[abi.MT_LATENCY] * len(units))
+    for pairwise in (abi.PW_ALL, abi.PW_MANN_WHITE, abi.PW_KRUSKAL, abi.PW_ANY):
+        p = full_params(oracle, algs=abi.ALG_MA_ALL, pairwise=pairwise)
+        got, _ = check_batch(ctx, oracle, b, p)
+    p = full_params(oracle, algs=abi.ALG_MA_ALL, pairwise=abi.PW_ALL)
+    got, _ = check_batch(ctx, oracle, b, p)
+    n = np.array([[len(u[1]), len(u[2])] for u in units], dtype=np.int64)
+    assert np.array_equal(got["mw_2u1"][:12] >= 0, np.ones(12, bool)) and np.all(got["mw_2u1"] <= 2 * n[:, 0] * n[:, 1])
+    assert int(got["mw_ties"][4]) == 1900 ** 3 - 1900              # one tie group of 1900
+    assert int(got["mw_2u1"][6]) == 2 * 700 * 700 and int(got["mw_2u1"][7]) == 0   # U of the baseline: all pairs / none
+    b.free()
