@@ -28,9 +28,7 @@ namespace {
 
 constexpr int kWarpsPerBlock = 8;
 
-// shared-memory index of sorted element e in the Wilcoxon kernel's tile: one pad word per 32 keeps the
-// warp's post-sort stores (lane stride R words) spread over the banks
-__host__ __device__ __forceinline__ int fm_pidx(int e) { return e + (e >> 5); }
+
 constexpr uint32_t kKeySentinel = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint32_t sel_minmax(bool lower, uint32_t a, uint32_t b) { return lower ? min(a, b) : max(a, b); }
@@ -147,74 +145,70 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsign
   }
 }
 
-// Tie bookkeeping of one sorted run stored in a shared-memory tile (element e at fm_pidx(e), the
-// lane owns elements lane*R .. lane*R+R-1, the first n are real).  Equal keys (after dropping the
-// low `sh` bits) form runs; for each run [s, s+t) the lane that holds its LAST element adds
-// t^3 - t to `ties`, stores t at rl[s] (if rl is given) and, for Wilcoxon keys (sign in bit 0,
-// positives first inside a run), adds cpos * (2s + t + 1) to `acc2` -- cpos positives at
-// twice-average-rank 2s + t + 1.  Two sweeps and two warp scans (run start / prefix count of
-// positives carried across lanes), uniform trip counts.  Only units that HAVE ties come here, so
-// it is a compact out-of-line routine (rolled loops over shared memory) rather than unrolled
-// register code: the kernel's instruction footprint is what limits its issue rate.
-template <bool PAD>
-__device__ __noinline__ void run_pass(const uint32_t *tile, const int R, const uint32_t sh, const bool wilcoxon,
-                                      const unsigned lane, const uint32_t n, uint16_t *rl, long long *ties_out,
-                                      long long *acc2_out) {
-  auto fm_pidx = [](int e) { return PAD ? ::fm_pidx(e) : e; };  // PAD = false: linear tile (k_mw)
-  const uint32_t base = lane * R;
-  const uint32_t prevk = (base && base - 1 <= n) ? tile[fm_pidx(base - 1)] : 0xFFFFFFFFu;
-  // sweep 1: last run start inside this lane, positives before it, positives in the lane
+// Tie bookkeeping of a sorted run that is still in registers (lane l holds elements l*R .. l*R+R-1, the
+// first n are real; keys compare equal after dropping their low `SH` bits).  Every element learns the first
+// and the last index of its run of equal keys -- a forward sweep with a max-scan of run heads over the lanes,
+// a backward sweep with a min-scan of run tails -- and contributes
+//   * fm_tie_step(i) = i*(i+1) to the tie sum, i = its index inside the run (3 * the sum = sum of t^3 - t);
+//   * if it is `counted` (Wilcoxon: a positive difference, sign bit 0 clear): its twice-average-rank
+//     2s + t + 1 = first + last + 2.
+// Only units that have ties come here.
+template <int R, int SH, bool RANKS>
+__device__ __forceinline__ void tie_sums(const uint32_t (&key)[R], const unsigned lane, const uint32_t n, uint32_t &tie_acc,
+                                         long long &rank2_acc) {
+  const int base = (int)(lane * R), rem = (int)n - base;  // real keys in this lane's slots (may be <= 0 or >= R)
+  const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1), prv = __shfl_up_sync(0xffffffffu, key[R - 1], 1);
+  // forward: last run head inside this lane, carried over the lanes
   int last_head = -1;
-  uint32_t ps_last = 0, pos_cnt = 0, gp = prevk >> sh;
+#pragma unroll
   for (int r = 0; r < R; ++r) {
-    const uint32_t e = base + r, k = e <= n ? tile[fm_pidx(e)] : 0xFFFFFFFFu, g = k >> sh;
-    if (e < n && (e == 0 || g != gp)) { last_head = (int)e; ps_last = pos_cnt; }
-    if (wilcoxon && e < n && !(k & 1u)) ++pos_cnt;
-    gp = g;
+    const bool head = r < rem && (r == 0 ? (lane == 0 || (key[0] >> SH) != (prv >> SH)) : (key[r] >> SH) != (key[r - 1] >> SH));
+    if (head) last_head = base + r;
   }
-  uint32_t pbase = pos_cnt;  // exclusive prefix sum of positives over lanes
+  int carry = last_head;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, pbase, o);
-    if ((int)lane >= o) pbase += t;
+    const int t = __shfl_up_sync(0xffffffffu, carry, o);
+    if ((int)lane >= o) carry = max(carry, t);
   }
-  pbase -= pos_cnt;
-  // run start (and positives before it) carried in from the nearest earlier lane that has one
-  int s_in = last_head;
-  uint32_t ps_in = pbase + ps_last;
+  int start = __shfl_up_sync(0xffffffffu, carry, 1);  // lane 0 never reads it: its first element is a head
+  // backward: first run tail inside this lane, carried back over the lanes
+  int first_tail = 0x7FFFFFFF;
+  if (RANKS) {
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int s2 = __shfl_up_sync(0xffffffffu, s_in, o);
-    const uint32_t p2 = __shfl_up_sync(0xffffffffu, ps_in, o);
-    if ((int)lane >= o && s2 > s_in) { s_in = s2; ps_in = p2; }
-  }
-  s_in = __shfl_up_sync(0xffffffffu, s_in, 1);
-  ps_in = __shfl_up_sync(0xffffffffu, ps_in, 1);
-  if (lane == 0) { s_in = -1; ps_in = 0; }
-  // sweep 2: close runs at their last element
-  int s_cur = s_in;
-  uint32_t ps_cur = ps_in, cnt = pbase;
-  long long ties = 0, acc2 = 0;
-  gp = prevk >> sh;
-  uint32_t k = base <= n ? tile[fm_pidx(base)] : 0xFFFFFFFFu;
-  for (int r = 0; r < R; ++r) {
-    const uint32_t e = base + r, g = k >> sh;
-    const uint32_t kn = e + 1 <= n ? tile[fm_pidx(e + 1)] : 0xFFFFFFFFu;  // slot n holds the sentinel
-    if (e < n) {
-      if (e == 0 || g != gp) { s_cur = (int)e; ps_cur = cnt; }
-      if (wilcoxon && !(k & 1u)) ++cnt;
-      if (e + 1 == n || g != (kn >> sh)) {
-        const long long t = (long long)e + 1 - s_cur;
-        if (rl) rl[s_cur] = (uint16_t)t;
-        if (wilcoxon) acc2 += (long long)(cnt - ps_cur) * (2ll * s_cur + t + 1);
-        if (t > 1) ties += t * t * t - t;
-      }
+    for (int r = R - 1; r >= 0; --r) {
+      const bool tail = r < rem && (base + r + 1 == (int)n || (r + 1 < R ? (key[r + 1] >> SH) != (key[r] >> SH) : (nxt >> SH) != (key[R - 1] >> SH)));
+      if (tail) first_tail = base + r;
     }
-    gp = g;
-    k = kn;
+    int back = first_tail;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_down_sync(0xffffffffu, back, o);
+      if ((int)lane + o < 32) back = min(back, t);
+    }
+    first_tail = __shfl_down_sync(0xffffffffu, back, 1);  // the nearest tail in the lanes after this one
   }
-  *ties_out = ties;
-  *acc2_out = acc2;
+  // per element: run start so far (forward), run end (from the element's own lane backwards, else the carry)
+  int ends[R];
+  if (RANKS) {
+    int end = first_tail;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r) {
+      const bool tail = r < rem && (base + r + 1 == (int)n || (r + 1 < R ? (key[r + 1] >> SH) != (key[r] >> SH) : (nxt >> SH) != (key[R - 1] >> SH)));
+      if (tail) end = base + r;
+      ends[r] = end;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    if (r < rem) {
+      const int e = base + r;
+      const bool head = r == 0 ? (lane == 0 || (key[0] >> SH) != (prv >> SH)) : (key[r] >> SH) != (key[r - 1] >> SH);
+      if (head) start = e;
+      tie_acc += fm_tie_step((uint32_t)(e - start));
+      if (RANKS && !(key[r] & 1u)) rank2_acc += (long long)(start + ends[r] + 2);
+    }
+  }
 }
 
 // p-values: same expressions, same order as oracle/DECISIONS.md "p-values".
@@ -256,7 +250,7 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
 
 // Wilcoxon signed-rank pass: one warp per unit, one sort of |d| keys (sign in bit 0).  The NEXT unit's
 // paired samples are staged in shared memory with 4-byte cp.async while the current unit is being
-// sorted in registers; tie-free units never touch the tile.  A separate launch from the Mann-Whitney
+// sorted in registers; ranks and the tie term are read off the sorted registers (tie_sums when there are ties).  A separate launch from the Mann-Whitney
 // pass: each keeps its instruction footprint inside the instruction cache (one fused kernel lost 4-5
 // issue slots per issued instruction to fetch stalls), and both are bound by instruction issue, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
@@ -264,14 +258,11 @@ template <int R>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxon(DevBatch b, const DevParams *__restrict__ dp,
                                                                                   fm_series_score *__restrict__ scores,
                                                                                   const int raw_cap) {
-  constexpr int kTile = 33 * R + 2;      // padded words of the sorted run (+ sentinel slot): compile-time, a run-time
-                                         // size cost this kernel registers and 18 % of its speed
-  extern __shared__ uint32_t s_tiles[];  // [warps][kTile] keys, then [warps][2][raw_cap] staged samples
+  extern __shared__ uint32_t s_tiles[];  // [warps][2][raw_cap] staged samples (the sorted keys never leave the registers)
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t pairwise = dp->pairwise;
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
-  uint32_t *const sB = s_tiles + (size_t)warp * kTile;
-  float *const rawA = reinterpret_cast<float *>(s_tiles + (size_t)kWarpsPerBlock * kTile) + (size_t)warp * 2 * raw_cap;
+  float *const rawA = reinterpret_cast<float *>(s_tiles) + (size_t)warp * 2 * raw_cap;
   float *const rawB = rawA + raw_cap;
   auto stage_pairs = [&](uint64_t uu) {
     if (uu < b.n_units) {
@@ -337,7 +328,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxo
       const uint32_t nxt = __shfl_down_sync(0xffffffffu, key[0], 1);
       tie = tie || (lane < 31 && ((key[R - 1] >> 1) == (nxt >> 1)) && (R < rem));
       const bool any_tie = __any_sync(0xffffffffu, tie);
-      long long acc = 0, tt = 0;
+      long long acc = 0;
+      uint32_t tie_acc = 0;
       if (!any_tie) {
         // tie-free |d|: the rank of sorted position e is e+1
         int a32 = 0, npos = 0;
@@ -346,19 +338,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxo
           if (r < rem && !(key[r] & 1u)) { a32 += 2 * (r + 1); ++npos; }
         acc = a32 + 2 * (int)(lane * R) * npos;
       } else {
-        // fm_pidx(lane*R + r) without a shift per key: the lane's slots start at pad0 and gain one pad
-        // word at each 32-element boundary they cross (slot `cross`, and cross + 32 when R > 32)
-        const int pad0 = fm_pidx((int)(lane * R)), cross = 32 - (int)((lane * R) & 31u);
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-          if (r <= rem) sB[pad0 + r + (r >= cross) + (R > 32 && r >= cross + 32)] = key[r];  // element n_valid is a sentinel already
-        if (n_valid == 32u * R && lane == 0) sB[fm_pidx(32 * R)] = kKeySentinel;
-        __syncwarp();
-        run_pass<true>(sB, R, 1u, true, lane, n_valid, nullptr, &tt, &acc);
-        __syncwarp();
+        tie_sums<R, 1, true>(key, lane, n_valid, tie_acc, acc);
       }
       w_2wp = warp_sum_i64(acc);
-      w_ties = any_tie ? warp_sum_i64(tt) : 0;
+      w_ties = any_tie ? 3 * warp_sum_i64((long long)tie_acc) : 0;
     }
     // exact integer statistics out; p-values and the combiner run one thread per unit in k_rank_finalize
     if (lane == 0 && have) {
@@ -706,7 +689,7 @@ cudaError_t launch_wilcoxon(const DevBatch &b, const DevParams *dp, uint32_t max
   const uint64_t blocks = std::min<uint64_t>((b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock, (uint64_t)sm_count * kBlocksPerSm);
   if (blocks == 0) return cudaSuccess;
   const int raw_cap = ((int)std::min<uint32_t>(max_pairs, 32u * R) + 3) & ~3;
-  const int smem = kWarpsPerBlock * ((33 * R + 2) * 4 + 2 * raw_cap * 4);
+  const int smem = kWarpsPerBlock * 2 * raw_cap * 4;
   cudaError_t e = cudaFuncSetAttribute(k_wilcoxon<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_wilcoxon<R><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, raw_cap);
