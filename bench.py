@@ -273,7 +273,7 @@ def run_ours(args):
                 t = res.timings_ms()
                 res.free()
                 if i >= 2:
-                    ts.append(t[key])
+                    ts.append(t[key] if key else t["setup"] + t["rank"] + t["band"] + t["verdict"])
             info = bb.info()
             bb.free()
             return sum(ts) / len(ts), info
@@ -307,6 +307,12 @@ def run_ours(args):
             ctx.score_host(h0, q, 1)
         other["cfg0_single_canary_job_5_series"] = {"us_per_call": (time.perf_counter() - t0) / 200 * 1e6,
                                                     "note": "fm_score_host small-job path: one upload, one clear, the launches, one download; no allocation"}
+        # cfg0's job shape at scale: what batching jobs buys (BrainWorker.process_many puts every open job document
+        # of a cycle into one batch).  200 000 canary jobs x 5 series x (60 + 30) points, MA band + Mann-Whitney U.
+        ms, info = timed(lambda: ctx.batch_synth(1_000_000, 0, 60, 30, units_per_service=5, n_metric_types=5,
+                                                 flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES), q, None, 4)
+        other["cfg0_shape_batched_200k_jobs"] = {"ms": ms, "jobs_per_s": 200_000 / (ms * 1e-3), "series_windows_per_s": 1_000_000 / (ms * 1e-3),
+                                                 "note": "one fm_score over 1 M units of 90 points; a job alone takes us_per_call above"}
         # ingest: Prometheus query_range response bodies -> sealed batch -> verdicts, cfg2's shape
         # (80 k series x 1440 points: 10 000 aliases with one 1380-point history series and eight 60-point current
         # series each), through fm_batch_add_prometheus_many on all host threads.  The same two bodies are lent
