@@ -638,3 +638,44 @@ def test_mann_whitney_search_kernel_extremes(ctx, oracle):
     assert int(got["mw_ties"][4]) == 1900 ** 3 - 1900              # one tie group of 1900
     assert int(got["mw_2u1"][6]) == 2 * 700 * 700 and int(got["mw_2u1"][7]) == 0   # U of the baseline: all pairs / none
     b.free()
+
+
+@pytest.mark.parametrize("window", [1, 2, 7, 30, 32, 33, 100])
+def test_rolling_band_filter_adversarial(ctx, oracle, window):
+    """The rolling band decides most points with a division-free filter and the rest with the oracle's exact
+    arithmetic (fm_band.cu roll_clear / roll_exact).  Series built to sit where a sloppy filter would differ from
+    the oracle: constant and two-valued windows (zero variance), huge offsets with tiny noise (cancellation in
+    the variance), tiny and huge magnitudes, points exactly ON the band edge of a two-point window, ramps, and
+    steps; every threshold from tight to loose, both bounds.  Counts and first indices must be bit-identical."""
+    rng = np.random.default_rng(1000 + window)
+    n_model, n_cur = 90, 150
+
+    def unit(x):
+        x = np.asarray(x, dtype=np.float32)
+        return (x[:n_model], np.empty(0, np.float32), x[n_model:n_model + n_cur])
+    t = np.arange(n_model + n_cur)
+    series = [
+        np.full(240, 5.0), np.zeros(240), np.full(240, -3.25),
+        np.where(t % 2 == 0, 1.0, 3.0), np.where(t % 3 == 0, 10.0, 10.5),
+        1e9 + rng.normal(0, 1, 240), 1e9 + rng.normal(0, 100, 240), -4e8 + rng.normal(0, 0.5, 240),
+        rng.normal(0, 1, 240) * 1e-30, rng.normal(0, 1, 240) * 1e30, rng.normal(5, 1, 240) * 1e-38,
+        t * 0.5, t * -2.0 + 7, np.where(t < 150, 1.0, 2.0), np.where(t < 130, 100.0, 100.0001),
+        np.round(rng.normal(50, 2, 240)), np.round(rng.normal(50, 0.6, 240)),
+        np.concatenate([np.full(120, 7.0), rng.normal(7, 1e-3, 120)]),
+        np.concatenate([rng.normal(7, 1e-3, 120), np.full(120, 7.0)]),
+        rng.normal(100, 5, 240), np.abs(rng.standard_cauchy(240)) * 3,
+    ]
+    # points exactly on the edge: after a window of two distinct values a and b the band edge with k = 1 and W = 2 is
+    # mean + sd = max(a, b) exactly (in exact arithmetic); many such pairs in a row
+    edge = np.tile(np.array([2.0, 4.0, 4.0, 2.0, 2.0, 4.0, 3.0, 5.0], np.float32), 30)
+    series.append(edge)
+    units = [unit(s) for s in series]
+    b = ctx.batch_from_units(units, service_id=[i // 4 for i in range(len(units))], metric_type=[i % 9 for i in range(len(units))])
+    for k, bound in ((0.0, abi.BOUND_BOTH), (0.5, abi.BOUND_BOTH), (1.0, abi.BOUND_UPPER), (1.0, abi.BOUND_BOTH), (2.0, abi.BOUND_LOWER),
+                     (3.0, abi.BOUND_BOTH), (10.0, abi.BOUND_BOTH), (1e6, abi.BOUND_BOTH)):
+        p = full_params(oracle, algs=abi.ALG_MA_ROLLING, pairwise=abi.PW_NONE)
+        p.ma_window = window
+        for mt in range(9):
+            p.rules[mt].threshold, p.rules[mt].bound, p.rules[mt].min_lower_bound = k, bound, (0.0 if mt % 2 else -1e30)
+        check_batch(ctx, oracle, b, p)
+    b.free()
