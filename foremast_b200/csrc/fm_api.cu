@@ -183,6 +183,15 @@ void resolve_params(const fm_params *p, DevParams *d) {
       for (int j = 0; j < 4; ++j) d->hw_pow[4 * i + j] = Q[j];
       mul(Q, Q, Q);
     }
+    double v[2] = {a, ab};  // A^(k-1-i) g for i = k-1 .. 0
+    for (int i = 0; i < 64; ++i) d->hw_w[2 * i] = d->hw_w[2 * i + 1] = 0.0;
+    for (int i = (int)std::min<uint32_t>(k, 64u) - 1; i >= 0; --i) {
+      d->hw_w[2 * i] = v[0];
+      d->hw_w[2 * i + 1] = v[1];
+      const double nl = A[0] * v[0] + A[1] * v[1], nb = A[2] * v[0] + A[3] * v[1];
+      v[0] = nl;
+      v[1] = nb;
+    }
   }
   for (int i = 0; i < FM_MAX_METRIC_TYPES; ++i) {
     const fm_metric_rule &r = p->rules[i].bound ? p->rules[i] : p->rules[0];  // D16

@@ -41,6 +41,9 @@ struct DevParams {
   // hw_pow[i] = A^(k*2^i), hw_lane[l] = A^(k*l), row-major
   double hw_pow[5 * 4];
   double hw_lane[32 * 4];
+  // hw_w[2i], hw_w[2i+1] = A^(k-1-i) g, g = (a, ab): what sample i of a k-sample chunk contributes to the
+  // level / trend at the end of the chunk (k_hw_tm's chunk offsets as one dot product per component)
+  double hw_w[2 * 64];
 };
 
 __device__ __forceinline__ unsigned fm_lane() { return threadIdx.x & 31u; }

@@ -20,6 +20,8 @@ with Context(0) as ctx:
             p.rules[mt].threshold, p.rules[mt].min_lower_bound, p.rules[mt].bound = 5.0, 0.0, abi.BOUND_UPPER
     p.algorithms = algs
     p.pairwise = pairwise
+    if os.environ.get("FM_PERIOD"):
+        p.period = int(os.environ["FM_PERIOD"])
     for _ in range(passes):
         r = ctx.score(b, p)
         v = r.verdicts()
