@@ -9,12 +9,17 @@
 // (256 KB per SM: 128 lanes x 512 32-bit columns, each thread of a warp reaching the columns of its
 // own lane with tcgen05.ld/st.32x32b) holds it as plain scratch -- no tensor-core instruction is
 // involved.  Shared memory then carries only the fp32 samples of the season (5.6 KB per unit) and
-// one CTA of 20 warps per SM runs 20 units at a time instead of 12.  Seasonals move between tensor
-// memory and registers eight at a time (16 columns), so the inner loops also lose their per-sample
-// LDS/STS and all of k_hw's wrap-around index handling (storage is indexed by the position inside
-// the lane's chunk, never by the absolute slot).  Seasons arrive by TMA: one cp.async.bulk per season
-// into one of two buffers with an mbarrier each (4-byte cp.async when source or size is not 16 B
-// aligned), the next season in flight while this one is scored.
+// one CTA of 18 warps per SM runs 18 units at a time instead of 12.  Seasonals move between tensor
+// memory and registers four at a time (8 columns), the next four requested before these are worked
+// on.  Seasons arrive by TMA: one cp.async.bulk per season into one of two buffers with an mbarrier
+// each (4-byte cp.async when source or size is not 16 B aligned), the next season in flight while
+// this one is scored, and the next unit's first two seasons pulled into L2 meanwhile.
+//
+// A season that lies wholly inside the model window -- all but the last one or two super-tiles of a
+// unit -- takes an unguarded path: the chunk offsets of pass 1 are a dot product with precomputed
+// weights (DevParams::hw_w), pass 2 is the plain one-step recurrence.  The super-tile the model window
+// ends in, the current samples and ragged ends take the guarded form, where a current sample whose
+// error is provably inside the band skips the band arithmetic.
 // Used when period % 32 == 0; other periods take k_hw.
 #include <algorithm>
 
@@ -27,63 +32,50 @@ constexpr int kMaxWarps = 18;  // measured: 16 -> 4.51, 18 -> 4.36, 19 -> 4.53, 
 using fm_hw::V2;
 using fm_hw::matvec;
 
-// eight seasonals = 16 columns of this thread's tensor-memory lane
-__device__ __forceinline__ void tm_ld8(uint32_t taddr, double (&d)[8]) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-#pragma unroll
-  for (int j = 0; j < 8; ++j) d[j] = __hiloint2double((int)r[2 * j + 1], (int)r[2 * j]);
+// ---- tensor memory: four seasonals = 8 columns of this thread's lane.  Load and arrival are apart:
+//      the next block is requested before this one is worked on and awaited after it.  The arrival
+//      names the registers as in/out operands, so nothing that reads them can move above it.
+__device__ __forceinline__ void tm_ld_issue(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
 }
-
-__device__ __forceinline__ void tm_st8(uint32_t taddr, const double (&d)[8]) {
-  uint32_t r[16];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    r[2 * j] = (uint32_t)__double2loint(d[j]);
-    r[2 * j + 1] = (uint32_t)__double2hiint(d[j]);
-  }
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};\n" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-      : "memory");
-}
-
-__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
-
-// The same 16 columns as raw words, load and arrival apart: the next block's seasonals are requested
-// before this block is worked on and awaited after it, so the tensor-memory round trip is hidden.
-// The arrival names the registers as in/out operands: nothing that reads them can move above it.
-__device__ __forceinline__ void tm_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tm_ld_arrive(uint32_t (&r)[16]) {
+__device__ __forceinline__ void tm_ld_arrive(uint32_t (&r)[8]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;\n"
-               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
-                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])
                :
                : "memory");
 }
-__device__ __forceinline__ void tm_st16(uint32_t taddr, const uint32_t (&r)[16]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};\n" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-      : "memory");
+__device__ __forceinline__ void tm_st(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};\n" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ double tm_get(const uint32_t (&r)[8], int j) {
+  return __hiloint2double((int)r[2 * j + 1], (int)r[2 * j]);
+}
+__device__ __forceinline__ void tm_put(uint32_t (&r)[8], int j, double v) {
+  r[2 * j] = (uint32_t)__double2loint(v);
+  r[2 * j + 1] = (uint32_t)__double2hiint(v);
+}
+__device__ __forceinline__ void tm_ld4(uint32_t taddr, double (&d)[4]) {  // load and wait
+  uint32_t r[8];
+  tm_ld_issue(taddr, r);
+  tm_ld_arrive(r);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) d[j] = tm_get(r, j);
+}
+__device__ __forceinline__ void tm_st4(uint32_t taddr, const double (&d)[4]) {
+  uint32_t r[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) tm_put(r, j, d[j]);
+  tm_st(taddr, r);
 }
 
-// ---- shared-memory reads at a register address + literal offset.  The sample and weight addresses of a
-//      lane are computed once and passed through keep(), otherwise the compiler re-derives them from
-//      threadIdx and the kernel parameters at every use (15 instructions per block of eight samples).
+// ---- shared-memory reads at a register address + literal offset.  The addresses a lane needs are
+//      computed once and passed through keep(): left alone, the compiler re-derives them from threadIdx
+//      and the kernel parameters at every use (15 instructions per block of samples).
 __device__ __forceinline__ uint32_t keep(uint32_t v) {
   asm volatile("" : "+r"(v));
   return v;
@@ -91,36 +83,27 @@ __device__ __forceinline__ uint32_t keep(uint32_t v) {
 #define FM_LDS_F32(dst, addr, imm) asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(dst) : "r"(addr), "n"(imm))
 #define FM_LDS_V2F64(dst, addr, imm) \
   asm volatile("ld.shared.v2.f64 {%0,%1}, [%2+%3];" : "=d"((dst).x), "=d"((dst).y) : "r"(addr), "n"(imm))
-__device__ __forceinline__ void lds8(uint32_t a, float (&x)[8]) {
+__device__ __forceinline__ void lds4(uint32_t a, float (&x)[4]) {
   FM_LDS_F32(x[0], a, 0); FM_LDS_F32(x[1], a, 4); FM_LDS_F32(x[2], a, 8); FM_LDS_F32(x[3], a, 12);
-  FM_LDS_F32(x[4], a, 16); FM_LDS_F32(x[5], a, 20); FM_LDS_F32(x[6], a, 24); FM_LDS_F32(x[7], a, 28);
 }
 __device__ __forceinline__ void ldw4(uint32_t a, double2 (&w)[4]) {
   FM_LDS_V2F64(w[0], a, 0); FM_LDS_V2F64(w[1], a, 16); FM_LDS_V2F64(w[2], a, 32); FM_LDS_V2F64(w[3], a, 48);
 }
-__device__ __forceinline__ double tm_get(const uint32_t (&r)[16], int j) {
-  return __hiloint2double((int)r[2 * j + 1], (int)r[2 * j]);
-}
-__device__ __forceinline__ void tm_put(uint32_t (&r)[16], int j, double v) {
-  r[2 * j] = (uint32_t)__double2loint(v);
-  r[2 * j + 1] = (uint32_t)__double2hiint(v);
-}
 
 // ---- TMA: one 1-D bulk copy (cp.async.bulk, UBLKCP) brings a whole season into shared memory and
-//      signals an mbarrier, instead of 45 four-byte cp.async per lane; needs 16 B aligned source and size
-__device__ __forceinline__ void mbar_init(uint64_t *bar) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+//      signals an mbarrier, instead of 45 four-byte cp.async per lane; needs 16 B aligned source and size.
+//      All shared operands are shared-window addresses.
+__device__ __forceinline__ void mbar_init(uint32_t bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void bulk_load(float *dst, const float *src, uint32_t bytes, uint64_t *bar) {
-  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar), d = (uint32_t)__cvta_generic_to_shared(dst);
+__device__ __forceinline__ void bulk_load(uint32_t dst, const float *src, uint32_t bytes, uint32_t bar) {
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // earlier generic reads of dst come first
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(d),
-               "l"(src), "r"(bytes), "r"(b)
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
@@ -129,9 +112,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "@p bra WAIT_DONE;\n"
       "bra WAIT_LOOP;\n"
       "WAIT_DONE:\n"
-      "}\n" ::"r"(b),
+      "}\n" ::"r"(bar),
       "r"(parity)
       : "memory");
+}
+__device__ __forceinline__ void cp_async4_s(uint32_t dst, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(gmem) : "memory");
 }
 
 // MODE as in fm_hw.cu: 0 score, 1 score + bands, 2 emit pass of the anomaly list, 3 fit (model
@@ -148,15 +134,16 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   constexpr bool BANDS = MODE == 1, EMIT = MODE == 2, FIT = MODE == 3, RESUME = MODE == 4;
   extern __shared__ float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
   __shared__ uint32_t s_tm_base;
-  __shared__ double s_apow[5 * 4];
-  __shared__ double2 s_w[64];  // chunk weights (DevParams::hw_w)
+  __shared__ double s_apow[5 * 4];    // A^(k*2^i), i = 0..4
+  __shared__ double s_alane[32 * 4];  // A^(k*lane)
+  __shared__ double2 s_w[64];         // chunk weights (DevParams::hw_w)
   __shared__ __align__(8) uint64_t s_bar[kMaxWarps][2];  // one mbarrier per warp per sample buffer
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-  const uint32_t m = dp->period, k = m / 32, kb = (k + 7) / 8;  // kb blocks of eight seasonals per lane
-  float *const Xb = s_x + (size_t)warp * 2 * m;
+  const uint32_t m = dp->period, k = m / 32;
+  const uint32_t kq = (k + 3) / 4;  // blocks of four seasonals per lane
 
   // ---- tensor memory: the CTA takes all 512 columns; warp w works in lane quarter w % 4 (the only
-  //      lanes its tcgen05.ld/st can reach) and column range (w / 4) * 16 * kb
+  //      lanes its tcgen05.ld/st can reach) and column range (w / 4) * 16 * ceil(k / 8)
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
                      (uint32_t)__cvta_generic_to_shared(&s_tm_base)),
@@ -164,29 +151,39 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
   }
   if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_pow[threadIdx.x];
+  if (threadIdx.x < 128) s_alane[threadIdx.x] = dp->hw_lane[threadIdx.x];
   if (threadIdx.x < 64) s_w[threadIdx.x] = make_double2(dp->hw_w[2 * threadIdx.x], dp->hw_w[2 * threadIdx.x + 1]);
+  const uint32_t bar_s = keep((uint32_t)__cvta_generic_to_shared(&s_bar[warp][0]));  // buffer 1's barrier: + 8
   if (lane == 0) {
-    mbar_init(&s_bar[warp][0]);
-    mbar_init(&s_bar[warp][1]);
+    mbar_init(bar_s);
+    mbar_init(bar_s + 8u);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;\n");
   const uint32_t tm_base = s_tm_base;
-  const uint32_t tS = tm_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * 16u * kb;
+  const uint32_t tS = keep(tm_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * 16u * ((k + 7) / 8));
 
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta, g1 = dp->gamma * (1.0 - dp->alpha);
-  const double *const Apow = s_apow;  // A^(k*2^i), i = 0..4
-  const double Alane[4] = {dp->hw_lane[4 * lane], dp->hw_lane[4 * lane + 1], dp->hw_lane[4 * lane + 2],
-                           dp->hw_lane[4 * lane + 3]};  // A^(k*lane)
   const uint32_t p0 = lane * k;  // this lane's chunk inside a season-long super-tile
-  const uint32_t xs0 = keep((uint32_t)__cvta_generic_to_shared(Xb + p0));  // ... as a shared-window address, buffer 0
-  const uint32_t ws0 = keep((uint32_t)__cvta_generic_to_shared(s_w));
   const uint32_t buf_bytes = m * 4u;
-  uint32_t par = 0, bulk = 0;    // per sample buffer: mbarrier phase to wait for next / filled by a bulk copy
+  const uint32_t xb_s = keep((uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * 2 * m));  // this warp's two buffers
+  const uint32_t xs0 = keep(xb_s + 4u * p0);                                                     // this lane's chunk in buffer 0
+  const uint32_t ws0 = keep((uint32_t)__cvta_generic_to_shared(s_w));
+  uint32_t pb = 0;  // bits 0-1: mbarrier phase to wait for next, per sample buffer; bits 2-3: buffer filled by a bulk copy
 
-  for (uint64_t u = (uint64_t)blockIdx.x * n_warps + warp; u < b.n_units; u += (uint64_t)gridDim.x * n_warps) {
+  const uint64_t stride_units = (uint64_t)gridDim.x * n_warps;
+  for (uint64_t u = (uint64_t)blockIdx.x * n_warps + warp; u < b.n_units; u += stride_units) {
+    {  // pull the head of this warp's next unit (its first two seasons) towards L2 while this unit is scored
+      const uint64_t un = u + stride_units;
+      if (un < b.n_units) {
+        const int64_t on = b.offsets[un], len = b.offsets[un + 1] - on;
+        const uint32_t bytes = (uint32_t)min((int64_t)(2u * m), len) * 4u;
+        const char *p = reinterpret_cast<const char *>(b.values + on);
+        for (uint32_t byte = lane * 128u; byte < bytes; byte += 32u * 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
+      }
+    }
     fm_hw::Unit w;
     if (!fm_hw::unit_begin<MODE>(b, dp, u, lane, m, scores, unit_status, unit_points, emit_off, state, w)) continue;
     const int64_t off = w.off;
@@ -199,58 +196,49 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     // size are 16 B aligned (the usual case: model window = history, whole seasons), else 4-byte
     // async copies, all in flight together.  Completion is awaited later (wait_buf).
     auto stage = [&](uint32_t q0s, uint32_t buf) {
-      float *const dst = Xb + buf * m;
+      const uint32_t dst = xb_s + (buf ? buf_bytes : 0u);
       const uint32_t nv = min(m, n_stream - q0s);
       if (q0s + nv <= ns || q0s >= ns) {  // one segment: one contiguous source
         const float *src = unit + (q0s < ns ? a0 + q0s : c0 + (q0s - ns));
         if (((reinterpret_cast<uintptr_t>(src) & 15u) | (nv & 3u)) == 0) {
-          if (lane == 0) bulk_load(dst, src, nv * 4u, &s_bar[warp][buf]);
-          bulk |= 1u << buf;
+          if (lane == 0) bulk_load(dst, src, nv * 4u, bar_s + 8u * buf);
+          pb |= 4u << buf;
           return;
         }
 #pragma unroll 3
-        for (uint32_t i = lane; i < nv; i += 32) cp_async4(dst + i, src + i);
+        for (uint32_t i = lane; i < nv; i += 32) cp_async4_s(dst + 4u * i, src + i);
       } else {
         for (uint32_t i = lane; i < nv; i += 32) {
           const uint32_t q = q0s + i;
-          cp_async4(dst + i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          cp_async4_s(dst + 4u * i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
         }
       }
       cp_async_commit();
-      bulk &= ~(1u << buf);
+      pb &= ~(4u << buf);
     };
     auto wait_buf = [&](uint32_t buf) {
-      if (bulk & (1u << buf)) {
-        mbar_wait(&s_bar[warp][buf], (par >> buf) & 1u);
-        par ^= 1u << buf;
+      if (pb & (4u << buf)) {
+        mbar_wait(bar_s + 8u * buf, (pb >> buf) & 1u);
+        pb ^= 1u << buf;
       } else {
         cp_async_wait<0>();
       }
       __syncwarp();
     };
-
-    V2 carry;
-    double sse = 0.0, sigma = 0.0;
-    bool sigma_ready = false;
-    uint32_t phase = 0;  // seasonal slot of stream position 0
-    uint32_t cur = 0;  // buffer that holds (or is receiving) the super-tile at q0
-    bool landed = false;
-    __syncwarp();      // the previous unit is done with both buffers
-    // sum of this lane's k samples of the season at shared address xa (two accumulators)
-    auto chunk_sum = [&](uint32_t xa) {
+    // sum over the season of the lane's k samples at shared address xa (two accumulators per lane)
+    auto season_sum = [&](uint32_t xa) {
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll 1
-      for (uint32_t blk = 0; blk < kb; ++blk, xa += 32u) {
-        float x[8];
-        lds8(xa, x);
-        const uint32_t rem = k - 8 * blk;  // warp-uniform
-        if (rem >= 8) {
-#pragma unroll
-          for (int jj = 0; jj < 8; jj += 2) { s0 += (double)x[jj]; s1 += (double)x[jj + 1]; }
+      for (uint32_t blk = 0; blk < kq; ++blk, xa += 16u) {
+        float x[4];
+        lds4(xa, x);
+        const uint32_t rem = k - 4 * blk;  // warp-uniform
+        if (rem >= 4) {
+          s0 += (double)x[0]; s1 += (double)x[1]; s0 += (double)x[2]; s1 += (double)x[3];
         } else {
 #pragma unroll
-          for (int jj = 0; jj < 7; ++jj)
-            if ((uint32_t)jj < rem) s0 += (double)x[jj];
+          for (int j = 0; j < 3; ++j)
+            if ((uint32_t)j < rem) s0 += (double)x[j];
         }
       }
       s0 += s1;
@@ -258,6 +246,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       for (int o = 16; o > 0; o >>= 1) s0 += __shfl_xor_sync(0xffffffffu, s0, o);
       return s0;
     };
+
+    V2 carry;
+    double sse = 0.0, sigma = 0.0;
+    bool sigma_ready = false;
+    uint32_t phase = 0;  // seasonal slot of stream position 0
+    uint32_t cur = 0;    // buffer that holds (or is receiving) the super-tile at q0
+    bool landed = false;
+    __syncwarp();        // the previous unit is done with both buffers
     if (RESUME) {
       stage(0, 0);
       carry.l = ust[0];
@@ -265,13 +261,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       sigma = ust[2];
       sigma_ready = true;
       phase = (uint32_t)ust[3];
-      uint32_t slot = phase + p0;  // < 2m: phase < m, p0 + i < m
+      uint32_t slot = phase + p0;  // < 2m: phase < m and p0 + i < m
 #pragma unroll 1
-      for (uint32_t blk = 0; blk < kb; ++blk) {
-        double s[8];
+      for (uint32_t blk = 0; blk < kq; ++blk) {
+        double s[4];
 #pragma unroll
-        for (int jj = 0; jj < 8; ++jj, ++slot) s[jj] = 8 * blk + jj < k ? ust[4 + (slot >= m ? slot - m : slot)] : 0.0;
-        tm_st8(tS + 16 * blk, s);
+        for (int j = 0; j < 4; ++j, ++slot) s[j] = 4 * blk + j < k ? ust[4 + (slot >= m ? slot - m : slot)] : 0.0;
+        tm_st4(tS + 8 * blk, s);
       }
     } else {
       // ---- initialisation from the first two seasons (D5); both lie inside the model window.  The
@@ -279,21 +275,21 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       stage(0, 0);
       stage(m, 1);
       wait_buf(0);
-      const double L0 = chunk_sum(xs0) / (double)m;
+      const double L0 = season_sum(xs0) / (double)m;
       {
         uint32_t xa = xs0;
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kb; ++blk, xa += 32u) {
-          float x[8];
-          lds8(xa, x);
-          double s[8];
+        for (uint32_t blk = 0; blk < kq; ++blk, xa += 16u) {
+          float x[4];
+          lds4(xa, x);
+          double s[4];
 #pragma unroll
-          for (int jj = 0; jj < 8; ++jj) s[jj] = 8 * blk + jj < k ? (double)x[jj] - L0 : 0.0;
-          tm_st8(tS + 16 * blk, s);
+          for (int j = 0; j < 4; ++j) s[j] = 4 * blk + j < k ? (double)x[j] - L0 : 0.0;
+          tm_st4(tS + 8 * blk, s);
         }
       }
       wait_buf(1);
-      const double M2 = chunk_sum(xs0 + buf_bytes) / (double)m;
+      const double M2 = season_sum(xs0 + buf_bytes) / (double)m;
       carry.l = L0;
       carry.b = (M2 - L0) / (double)m;
       cur = 1;
@@ -301,6 +297,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     }
     tm_wait_st();
     uint32_t n_anom = 0, first = FM_NONE_IDX;
+
     for (uint32_t q0 = RESUME ? 0u : m; q0 < n_stream; q0 += m, cur ^= 1u) {
       // wait for this super-tile; every lane is then done with the other buffer: start the next one
       if (landed) { landed = false; __syncwarp(); }
@@ -308,69 +305,47 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       if (q0 + m < n_stream) stage(q0 + m, cur ^ 1u);
       const uint32_t qa = q0 + p0;                                      // stream position of the chunk
       const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
-      const float *const xp = Xb + cur * m + p0;
-      const uint32_t xs = keep(xs0 + (cur ? buf_bytes : 0u));  // the chunk's samples as a shared-window address
-      // A whole season inside the model window (all but the last one or two super-tiles of a unit) is the
-      // fast case: every lane has its k samples and only the residual sum is wanted, so nothing is guarded
-      // per lane; seasonals come eight at a time, the next block requested before this one is worked on.
-      // Every other super-tile (the one the model window ends in, the current samples, a ragged end) takes
-      // the guarded form.
-      const bool whole = !RESUME && q0 + m <= ns;  // warp-uniform
-      uint32_t ra[16], rb[16];
+      const uint32_t xs = keep(xs0 + (cur ? buf_bytes : 0u));          // the chunk's samples (shared-window address)
+      const bool whole = !RESUME && q0 + m <= ns;  // a whole season of the model window (warp-uniform)
+      uint32_t ra[8], rb[8];
 
-      // ---- pass 1: chunk offset from a zero state.  Fast case: a dot product with the precomputed
-      //      chunk weights (two accumulators per component, no dependent chain).  Chunks past the end of
-      //      the stream only feed lanes that are past the end too.
+      // ---- pass 1: chunk offset from a zero state.  Whole season: a dot product with the chunk weights
+      //      (two accumulators per component, no dependent chain).  Chunks past the end of the stream only
+      //      feed lanes that are past the end too.
       V2 uo;
       if (whole) {
         double ul0 = 0.0, ub0 = 0.0, ul1 = 0.0, ub1 = 0.0;
-        auto p1 = [&](uint32_t blk, uint32_t (&c)[16], uint32_t (&n)[16]) {
-          const uint32_t xa = xs + 32u * blk, wa = ws0 + 128u * blk, rem = k - 8u * blk;
+        auto p1 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
+          float x[4];
+          double2 wv[4];
+          lds4(xs + 16u * blk, x);
+          ldw4(ws0 + 64u * blk, wv);
           tm_ld_arrive(c);
-          if (blk + 1 < kb) tm_ld16_issue(tS + 16 * (blk + 1), n);
-          float x[8];
-          lds8(xa, x);
-          double2 wA[4], wB[4];
-          ldw4(wa, wA);
-          if (rem >= 8) {
-            ldw4(wa + 64u, wB);
+          if (blk + 1 < kq) tm_ld_issue(tS + 8 * (blk + 1), n);
+          const uint32_t rem = k - 4u * blk;  // warp-uniform
+          if (rem >= 4) {
+            const double y0 = (double)x[0] - tm_get(c, 0), y1 = (double)x[1] - tm_get(c, 1);
+            const double y2 = (double)x[2] - tm_get(c, 2), y3 = (double)x[3] - tm_get(c, 3);
+            ul0 = fma(wv[0].x, y0, ul0); ub0 = fma(wv[0].y, y0, ub0);
+            ul1 = fma(wv[1].x, y1, ul1); ub1 = fma(wv[1].y, y1, ub1);
+            ul0 = fma(wv[2].x, y2, ul0); ub0 = fma(wv[2].y, y2, ub0);
+            ul1 = fma(wv[3].x, y3, ul1); ub1 = fma(wv[3].y, y3, ub1);
+          } else {
 #pragma unroll
-            for (int jj = 0; jj < 4; jj += 2) {
-              const double y0 = (double)x[jj] - tm_get(c, jj), y1 = (double)x[jj + 1] - tm_get(c, jj + 1);
-              ul0 = fma(wA[jj].x, y0, ul0); ub0 = fma(wA[jj].y, y0, ub0);
-              ul1 = fma(wA[jj + 1].x, y1, ul1); ub1 = fma(wA[jj + 1].y, y1, ub1);
-            }
-#pragma unroll
-            for (int jj = 0; jj < 4; jj += 2) {
-              const double y0 = (double)x[4 + jj] - tm_get(c, 4 + jj), y1 = (double)x[5 + jj] - tm_get(c, 5 + jj);
-              ul0 = fma(wB[jj].x, y0, ul0); ub0 = fma(wB[jj].y, y0, ub0);
-              ul1 = fma(wB[jj + 1].x, y1, ul1); ub1 = fma(wB[jj + 1].y, y1, ub1);
-            }
-          } else {  // the last block of a chunk whose length is not a multiple of eight; rem is warp-uniform
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              if ((uint32_t)jj < rem) {
-                const double y0 = (double)x[jj] - tm_get(c, jj);
-                ul0 = fma(wA[jj].x, y0, ul0); ub0 = fma(wA[jj].y, y0, ub0);
-              }
-            }
-            if (rem > 4) {
-              ldw4(wa + 64u, wB);
-#pragma unroll
-              for (int jj = 0; jj < 3; ++jj) {
-                if ((uint32_t)(4 + jj) < rem) {
-                  const double y0 = (double)x[4 + jj] - tm_get(c, 4 + jj);
-                  ul0 = fma(wB[jj].x, y0, ul0); ub0 = fma(wB[jj].y, y0, ub0);
-                }
+            for (int j = 0; j < 3; ++j) {
+              if ((uint32_t)j < rem) {
+                const double y = (double)x[j] - tm_get(c, j);
+                ul0 = fma(wv[j].x, y, ul0);
+                ub0 = fma(wv[j].y, y, ub0);
               }
             }
           }
         };
-        tm_ld16_issue(tS, ra);
+        tm_ld_issue(tS, ra);
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kb; blk += 2) {
+        for (uint32_t blk = 0; blk < kq; blk += 2) {
           p1(blk, ra, rb);
-          if (blk + 1 < kb) p1(blk + 1, rb, ra);
+          if (blk + 1 < kq) p1(blk + 1, rb, ra);
         }
         uo.l = ul0 + ul1;
         uo.b = ub0 + ub1;
@@ -378,16 +353,16 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         uo.l = 0.0;
         uo.b = 0.0;
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kb; ++blk) {
-          if (__all_sync(0xffffffffu, 8 * blk >= kv)) break;  // no lane has samples from here on
-          double s[8];
-          float x[8];
-          lds8(xs + 32u * blk, x);
-          tm_ld8(tS + 16 * blk, s);
+        for (uint32_t blk = 0; blk < kq; ++blk) {
+          if (__all_sync(0xffffffffu, 4 * blk >= kv)) break;  // no lane has samples from here on
+          float x[4];
+          double s[4];
+          lds4(xs + 16u * blk, x);
+          tm_ld4(tS + 8 * blk, s);
 #pragma unroll
-          for (int jj = 0; jj < 8; ++jj) {
-            if (8 * blk + jj < kv) {
-              const double y = (double)x[jj] - s[jj];
+          for (int j = 0; j < 4; ++j) {
+            if (4 * blk + j < kv) {
+              const double y = (double)x[j] - s[j];
               const double t = uo.l + uo.b, d = y - t;
               uo.l = fma(alpha, d, t);
               uo.b = fma(ab, d, uo.b);
@@ -396,50 +371,50 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
       }
       // ---- the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
-      const V2 vin = fm_hw::scan_chunks(uo, carry, Apow, Alane, lane);
+      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, s_alane + 4 * lane, lane);
 
       // ---- pass 2: the real recurrence over the chunk
       double l = vin.l, bb = vin.b;
       unsigned long long fmask = 0ull;  // flags of the chunk's current samples (k <= 64)
       const bool tile_has_cur = q0 + m > ns;
       if (whole) {
-        auto one = [&](float xf, uint32_t (&c)[16], int jj) {
-          const double sv = tm_get(c, jj);
+        auto one = [&](float xf, uint32_t (&c)[8], int j) {
+          const double sv = tm_get(c, j);
           const double y = (double)xf - sv;
           const double lb = l + bb, e = y - lb;
           l = fma(alpha, e, lb);
           bb = fma(ab, e, bb);
           sse = fma(e, e, sse);
-          tm_put(c, jj, fma(g1, e, sv));
+          tm_put(c, j, fma(g1, e, sv));
         };
-        auto p2 = [&](uint32_t blk, uint32_t (&c)[16], uint32_t (&n)[16]) {
-          const uint32_t rem = k - 8u * blk;
+        auto p2 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
+          float x[4];
+          lds4(xs + 16u * blk, x);
           tm_ld_arrive(c);
-          if (blk + 1 < kb) tm_ld16_issue(tS + 16 * (blk + 1), n);
-          float x[8];
-          lds8(xs + 32u * blk, x);
-          if (rem >= 8) {
+          if (blk + 1 < kq) tm_ld_issue(tS + 8 * (blk + 1), n);
+          const uint32_t rem = k - 4u * blk;
+          if (rem >= 4) {
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) one(x[jj], c, jj);
+            for (int j = 0; j < 4; ++j) one(x[j], c, j);
           } else {
 #pragma unroll
-            for (int jj = 0; jj < 7; ++jj)
-              if ((uint32_t)jj < rem) one(x[jj], c, jj);
+            for (int j = 0; j < 3; ++j)
+              if ((uint32_t)j < rem) one(x[j], c, j);
           }
-          tm_st16(tS + 16 * blk, c);
+          tm_st(tS + 8 * blk, c);
         };
-        tm_ld16_issue(tS, ra);
+        tm_ld_issue(tS, ra);
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kb; blk += 2) {
+        for (uint32_t blk = 0; blk < kq; blk += 2) {
           p2(blk, ra, rb);
-          if (blk + 1 < kb) p2(blk + 1, rb, ra);
+          if (blk + 1 < kq) p2(blk + 1, rb, ra);
         }
         tm_wait_st();
       } else {
         // Sweep 0 takes the samples of the model window, sweep 1 the current ones (sigma must be final
         // first); each sweep walks the seasonals block by block through registers.
         const uint32_t i_m = qa < ns ? min(kv, ns - qa) : 0u;  // model samples at the head of the chunk
-        double clear = 0.0;  // |x - forecast| up to this is inside the band whatever the rounding (see below)
+        double clear = 0.0;  // a current sample with |x - forecast| up to this is inside the band (see below)
 #pragma unroll 1
         for (int sweep = 0; sweep < 2; ++sweep) {
           if (sweep == 0 && q0 >= ns) continue;  // nothing of the model window in this super-tile
@@ -456,18 +431,18 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           }
           const uint32_t lo = sweep ? i_m : 0u, hi = sweep ? kv : i_m;
 #pragma unroll 1
-          for (uint32_t blk = 0; blk < kb; ++blk) {
-            if (__all_sync(0xffffffffu, 8 * blk >= hi || 8 * blk + 8 <= lo)) continue;  // no lane has work in this block
-            double s[8];
-            float xf[8];
-            lds8(xs + 32u * blk, xf);
-            tm_ld8(tS + 16 * blk, s);
+          for (uint32_t blk = 0; blk < kq; ++blk) {
+            if (__all_sync(0xffffffffu, 4 * blk >= hi || 4 * blk + 4 <= lo)) continue;  // no lane has work in this block
+            float xf[4];
+            double s[4];
+            lds4(xs + 16u * blk, xf);
+            tm_ld4(tS + 8 * blk, s);
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) {
-              const uint32_t i = 8 * blk + jj;
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t i = 4 * blk + j;
               if (i >= lo && i < hi) {  // one sample: one-step error, state and season update, residual sum or flag
-                const double x = (double)xf[jj];
-                const double lb = l + bb, f = lb + s[jj], e = x - f;
+                const double x = (double)xf[j];
+                const double lb = l + bb, f = lb + s[j], e = x - f;
                 l = fma(alpha, e, lb);
                 bb = fma(ab, e, bb);
                 if (sweep == 0) {
@@ -488,10 +463,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
                     band_lo[off + c0 + (qa + i - ns)] = (float)lw;
                   }
                 }
-                s[jj] = fma(g1, e, s[jj]);
+                s[j] = fma(g1, e, s[j]);
               }
             }
-            tm_st8(tS + 16 * blk, s);
+            tm_st4(tS + 8 * blk, s);
           }
           tm_wait_st();
         }
@@ -504,7 +479,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         carry.l = __shfl_sync(0xffffffffu, l, src);
         carry.b = __shfl_sync(0xffffffffu, bb, src);
       }
-      if (tile_has_cur) fm_hw::tile_flags<EMIT>(fmask, lane, qa, ns, w.emit_base, emit_idx, emit_val, xp, n_anom, first);
+      if (tile_has_cur) {
+        const float *const xp = s_x + (size_t)warp * 2 * m + cur * m + p0;
+        fm_hw::tile_flags<EMIT>(fmask, lane, qa, ns, w.emit_base, emit_idx, emit_val, xp, n_anom, first);
+      }
     }
     if (FIT || RESUME) {  // save the model: state after the last sample, residual sigma, phase, seasonals
       if (FIT && !sigma_ready) {
@@ -513,14 +491,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         sigma = sqrt(t / (double)(ns - m));
       }
-      for (uint32_t blk = 0; blk < kb; ++blk) {
-        double s[8];
-        tm_ld8(tS + 16 * blk, s);
+      uint32_t slot = phase + p0;
+#pragma unroll 1
+      for (uint32_t blk = 0; blk < kq; ++blk) {
+        double s[4];
+        tm_ld4(tS + 8 * blk, s);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t i = 8 * blk + j;
-          if (i < k) ust[4 + (phase + p0 + i) % m] = s[j];
-        }
+        for (int j = 0; j < 4; ++j, ++slot)
+          if (4 * blk + j < k) ust[4 + (slot >= m ? slot - m : slot)] = s[j];
       }
       if (lane == 0) fm_hw::save_state_scalars(ust, carry, sigma, phase, n_stream, m);
       __syncwarp();
@@ -549,7 +527,7 @@ cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, f
   const uint64_t cap = (uint64_t)sm_count;  // persistent: one CTA is resident per SM (it owns the tensor memory)
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  const int smem = warps * 2 * (int)period * (int)sizeof(float) + 32;  // lds8 may read up to 7 samples past a chunk
+  const int smem = warps * 2 * (int)period * (int)sizeof(float) + 32;  // lds4 may read up to 3 samples past a chunk
   cudaError_t e = cudaFuncSetAttribute(k_hw_tm<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_hw_tm<MODE><<<(unsigned)blocks, warps * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
