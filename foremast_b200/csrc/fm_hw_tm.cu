@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
   const uint32_t m = dp->period, k = m / 32;
   const uint32_t kq = (k + 3) / 4;  // blocks of four seasonals per lane
+  const uint32_t npair = min(k / 8, (kq - 1) / 2);  // leading pairs of whole blocks that have a block after them
 
   // ---- tensor memory: the CTA takes all 512 columns; warp w works in lane quarter w % 4 (the only
   //      lanes its tcgen05.ld/st can reach) and column range (w / 4) * 16 * ceil(k / 8)
@@ -175,15 +176,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
 
   const uint64_t stride_units = (uint64_t)gridDim.x * n_warps;
   for (uint64_t u = (uint64_t)blockIdx.x * n_warps + warp; u < b.n_units; u += stride_units) {
-    {  // pull the head of this warp's next unit (its first two seasons) towards L2 while this unit is scored
-      const uint64_t un = u + stride_units;
-      if (un < b.n_units) {
-        const int64_t on = b.offsets[un], len = b.offsets[un + 1] - on;
-        const uint32_t bytes = (uint32_t)min((int64_t)(2u * m), len) * 4u;
-        const char *p = reinterpret_cast<const char *>(b.values + on);
-        for (uint32_t byte = lane * 128u; byte < bytes; byte += 32u * 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
-      }
-    }
     fm_hw::Unit w;
     if (!fm_hw::unit_begin<MODE>(b, dp, u, lane, m, scores, unit_status, unit_points, emit_off, state, w)) continue;
     const int64_t off = w.off;
@@ -303,6 +295,15 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       if (landed) { landed = false; __syncwarp(); }
       else wait_buf(cur);
       if (q0 + m < n_stream) stage(q0 + m, cur ^ 1u);
+      if (q0 + m >= n_stream) {  // last super-tile: pull the head of this warp's next unit (its first two seasons) towards L2
+        const uint64_t un = u + stride_units;
+        if (un < b.n_units) {
+          const int64_t on = b.offsets[un], len = b.offsets[un + 1] - on;
+          const uint32_t bytes = (uint32_t)min((int64_t)(2u * m), len) * 4u;
+          const char *p = reinterpret_cast<const char *>(b.values + on);
+          for (uint32_t byte = lane * 128u; byte < bytes; byte += 32u * 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + byte));
+        }
+      }
       const uint32_t qa = q0 + p0;                                      // stream position of the chunk
       const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
       const uint32_t xs = keep(xs0 + (cur ? buf_bytes : 0u));          // the chunk's samples (shared-window address)
@@ -341,9 +342,29 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
             }
           }
         };
+        // the leading pairs of blocks are whole and have a block after them: no guards at all
+        auto p1w = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
+          float x[4];
+          double2 wv[4];
+          lds4(xs + 16u * blk, x);
+          ldw4(ws0 + 64u * blk, wv);
+          tm_ld_arrive(c);
+          tm_ld_issue(tS + 8 * (blk + 1), n);
+          const double y0 = (double)x[0] - tm_get(c, 0), y1 = (double)x[1] - tm_get(c, 1);
+          const double y2 = (double)x[2] - tm_get(c, 2), y3 = (double)x[3] - tm_get(c, 3);
+          ul0 = fma(wv[0].x, y0, ul0); ub0 = fma(wv[0].y, y0, ub0);
+          ul1 = fma(wv[1].x, y1, ul1); ub1 = fma(wv[1].y, y1, ub1);
+          ul0 = fma(wv[2].x, y2, ul0); ub0 = fma(wv[2].y, y2, ub0);
+          ul1 = fma(wv[3].x, y3, ul1); ub1 = fma(wv[3].y, y3, ub1);
+        };
         tm_ld_issue(tS, ra);
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kq; blk += 2) {
+        for (uint32_t blk = 0; blk < 2 * npair; blk += 2) {
+          p1w(blk, ra, rb);
+          p1w(blk + 1, rb, ra);
+        }
+#pragma unroll 1
+        for (uint32_t blk = 2 * npair; blk < kq; blk += 2) {
           p1(blk, ra, rb);
           if (blk + 1 < kq) p1(blk + 1, rb, ra);
         }
@@ -403,9 +424,23 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           }
           tm_st(tS + 8 * blk, c);
         };
+        auto p2w = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
+          float x[4];
+          lds4(xs + 16u * blk, x);
+          tm_ld_arrive(c);
+          tm_ld_issue(tS + 8 * (blk + 1), n);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) one(x[j], c, j);
+          tm_st(tS + 8 * blk, c);
+        };
         tm_ld_issue(tS, ra);
 #pragma unroll 1
-        for (uint32_t blk = 0; blk < kq; blk += 2) {
+        for (uint32_t blk = 0; blk < 2 * npair; blk += 2) {
+          p2w(blk, ra, rb);
+          p2w(blk + 1, rb, ra);
+        }
+#pragma unroll 1
+        for (uint32_t blk = 2 * npair; blk < kq; blk += 2) {
           p2(blk, ra, rb);
           if (blk + 1 < kq) p2(blk + 1, rb, ra);
         }
