@@ -9,7 +9,7 @@
 // (256 KB per SM: 128 lanes x 512 32-bit columns, each thread of a warp reaching the columns of its
 // own lane with tcgen05.ld/st.32x32b) holds it as plain scratch -- no tensor-core instruction is
 // involved.  Shared memory then carries only the fp32 samples of the season (5.6 KB per unit) and
-// one CTA of 18 warps per SM runs 18 units at a time instead of 12.  Seasonals move between tensor
+// one CTA of 20 warps per SM runs 20 units at a time instead of 12.  Seasonals move between tensor
 // memory and registers four at a time (8 columns), the next four requested before these are worked
 // on.  Seasons arrive by TMA: one cp.async.bulk per season into one of two buffers with an mbarrier
 // each (4-byte cp.async when source or size is not 16 B aligned), the next season in flight while
@@ -27,7 +27,7 @@
 
 namespace {
 
-constexpr int kMaxWarps = 18;  // measured: 16 -> 4.51, 18 -> 4.36, 19 -> 4.53, 20 (single sample buffer) -> 5.07 ms per 200k x 10080
+constexpr int kMaxWarps = 20;  // per 200k x 10080: 18 -> 3.30, 19 -> 3.15, 20 -> 3.01 ms (tensor memory holds 20 x 96 columns, shared memory 20 x 2 seasons)
 
 using fm_hw::V2;
 using fm_hw::matvec;
@@ -135,7 +135,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   extern __shared__ float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
   __shared__ uint32_t s_tm_base;
   __shared__ double s_apow[5 * 4];    // A^(k*2^i), i = 0..4
-  __shared__ double s_alane[32 * 4];  // A^(k*lane)
   __shared__ double2 s_w[64];         // chunk weights (DevParams::hw_w)
   __shared__ __align__(8) uint64_t s_bar[kMaxWarps][2];  // one mbarrier per warp per sample buffer
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
@@ -152,7 +151,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
   }
   if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_pow[threadIdx.x];
-  if (threadIdx.x < 128) s_alane[threadIdx.x] = dp->hw_lane[threadIdx.x];
   if (threadIdx.x < 64) s_w[threadIdx.x] = make_double2(dp->hw_w[2 * threadIdx.x], dp->hw_w[2 * threadIdx.x + 1]);
   const uint32_t bar_s = keep((uint32_t)__cvta_generic_to_shared(&s_bar[warp][0]));  // buffer 1's barrier: + 8
   if (lane == 0) {
@@ -392,7 +390,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
       }
       // ---- the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
-      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, s_alane + 4 * lane, lane);
+      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, dp->hw_lane + 4 * lane, lane);
 
       // ---- pass 2: the real recurrence over the chunk
       double l = vin.l, bb = vin.b;
@@ -556,7 +554,7 @@ cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, f
   // warps per CTA: four lane quarters x as many 16*kb-column ranges as fit in 512 columns, capped by
   // the launch bound and by the fp32 season each warp keeps in shared memory
   int warps = (int)std::min<uint32_t>(4 * (512 / (16 * kb)), kMaxWarps);
-  warps = std::min(warps, (220 * 1024 - 32) / ((int)period * 8));
+  warps = std::min(warps, (227 * 1024 - 1536 - 32) / ((int)period * 8));  // 1.5 KB: the kernel's static shared memory
   if (warps < 1) return cudaErrorInvalidValue;
   uint64_t blocks = (b.n_units + warps - 1) / warps;
   const uint64_t cap = (uint64_t)sm_count;  // persistent: one CTA is resident per SM (it owns the tensor memory)
