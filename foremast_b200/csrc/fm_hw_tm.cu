@@ -308,11 +308,15 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       const bool whole = !RESUME && q0 + m <= ns;  // a whole season of the model window (warp-uniform)
       uint32_t ra[8], rb[8];
 
-      // ---- pass 1: chunk offset from a zero state.  Whole season: a dot product with the chunk weights
-      //      (two accumulators per component, no dependent chain).  Chunks past the end of the stream only
-      //      feed lanes that are past the end too.
+      // ---- pass 1: chunk offset from a zero state, as a dot product with the chunk weights (two
+      //      accumulators per component, no dependent chain).  The weights are those of a FULL chunk, and that
+      //      is enough: an offset is only ever used by the lanes after it, and the one chunk of a super-tile
+      //      that can be short is the last one with samples (whatever this computes there, and in the empty
+      //      chunks behind it, only reaches lanes that have no samples).  Skipped when one lane holds it all.
       V2 uo;
-      if (whole) {
+      uo.l = 0.0;
+      uo.b = 0.0;
+      if (min(m, n_stream - q0) > k) {
         double ul0 = 0.0, ub0 = 0.0, ul1 = 0.0, ub1 = 0.0;
         auto p1 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
           float x[4];
@@ -368,26 +372,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
         uo.l = ul0 + ul1;
         uo.b = ub0 + ub1;
-      } else {
-        uo.l = 0.0;
-        uo.b = 0.0;
-#pragma unroll 1
-        for (uint32_t blk = 0; blk < kq; ++blk) {
-          if (__all_sync(0xffffffffu, 4 * blk >= kv)) break;  // no lane has samples from here on
-          float x[4];
-          double s[4];
-          lds4(xs + 16u * blk, x);
-          tm_ld4(tS + 8 * blk, s);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (4 * blk + j < kv) {
-              const double y = (double)x[j] - s[j];
-              const double t = uo.l + uo.b, d = y - t;
-              uo.l = fma(alpha, d, t);
-              uo.b = fma(ab, d, uo.b);
-            }
-          }
-        }
       }
       // ---- the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
       const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, dp->hw_lane + 4 * lane, lane);
