@@ -380,6 +380,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       double l = vin.l, bb = vin.b;
       unsigned long long fmask = 0ull;  // flags of the chunk's current samples (k <= 64)
       const bool tile_has_cur = q0 + m > ns;
+      if (!sigma_ready && q0 >= ns) {  // the model window ended with the previous super-tile: close the residual sum
+        double t = sse;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        sigma = sqrt(t / (double)(ns - m));
+        sigma_ready = true;
+      }
       if (whole) {
         auto one = [&](float xf, uint32_t (&c)[8], int j) {
           const double sv = tm_get(c, j);
@@ -427,6 +434,40 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           if (blk + 1 < kq) p2(blk + 1, rb, ra);
         }
         tm_wait_st();
+      } else if (!FIT && !RESUME && sigma_ready && q0 >= ns && q0 + m >= n_stream) {
+        // The unit's last super-tile, current samples only, and no state is kept afterwards: the seasonals
+        // are dead after this read, and so are level and trend after a lane's last real sample.  So nothing
+        // is guarded per lane (what a lane computes past its samples is masked out of the flags) and nothing
+        // is written back.
+        const double clear = kk * sigma * 0.999999;  // see the guarded form below
+        const uint32_t kmax = min(k, n_stream - q0);  // the longest chunk of the super-tile (lane 0's)
+#pragma unroll 1
+        for (uint32_t blk = 0; 4 * blk < kmax; ++blk) {
+          float xf[4];
+          double s[4];
+          lds4(xs + 16u * blk, xf);
+          tm_ld4(tS + 8 * blk, s);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t i = 4 * blk + j;
+            const double x = (double)xf[j];
+            const double lb = l + bb, f = lb + s[j], e = x - f;
+            l = fma(alpha, e, lb);
+            bb = fma(ab, e, bb);
+            if (BANDS || !(fabs(e) <= clear && x >= mlb)) {
+              const double up = fma(kk, sigma, f);
+              double lw = fma(-kk, sigma, f);
+              lw = lw < mlb ? mlb : lw;
+              const double gx = 1e-9 * (fabs(f) + fabs(x));
+              if (((bound & 1u) && x - up > gx) || ((bound & 2u) && lw - x > gx)) fmask |= 1ull << i;
+              if (BANDS && i < kv) {
+                band_up[off + c0 + (qa + i - ns)] = (float)up;
+                band_lo[off + c0 + (qa + i - ns)] = (float)lw;
+              }
+            }
+          }
+        }
+        fmask &= kv >= 64 ? ~0ull : (1ull << kv) - 1ull;
       } else {
         // Sweep 0 takes the samples of the model window, sweep 1 the current ones (sigma must be final
         // first); each sweep walks the seasonals block by block through registers.
