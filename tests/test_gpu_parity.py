@@ -223,6 +223,42 @@ def test_holt_winters(ctx, oracle, shape, period, n, seasonals, monkeypatch):
     b.free()
 
 
+@pytest.mark.parametrize("period,shape", [(256, (1041, 0, 133)), (384, (1553, 0, 200)), (512, (2065, 7, 600)),
+                                          (1024, (4113, 0, 40)), (1440, (4320, 0, 1440)), (1440, (5000, 0, 3000)),
+                                          (64, (300, 0, 1)), (2048, (6200, 0, 2100))])
+def test_holt_winters_tile_classes(ctx, oracle, period, shape):
+    """k_hw_tm takes different paths for a whole season of the model window, for the super-tile the model
+    window ends in, for whole and ragged super-tiles of current samples and for the last super-tile of a
+    unit, and its blocks of four seasonals end differently for every chunk length (period / 32 = 8, 12,
+    16, 32, 45, 2, 64 here).  Scores, bands and the anomaly list against the oracle on each."""
+    n = 120
+    b = ctx.batch_synth(n, *shape, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=period + shape[2])
+    p = full_params(oracle, abi.ALG_HW, abi.PW_NONE)
+    p.period = period
+    got, worst = check_batch(ctx, oracle, b, p)
+    ran = (got["status"] >> (abi.S_ALG_SHIFT + 4)) & 1
+    assert ran.mean() > 0.5
+    p.band_algorithm = abi.ALG_HW
+    host = b.download()
+    ref, up, lo = oracle.score(host, p, want_bands=True)
+    res = ctx.score(b, p)
+    for u in (0, n // 3, n - 1):
+        gu, gl = res.bands(u)
+        o = int(host.offsets[u]) + int(host.seg_lens[u][0]) + int(host.seg_lens[u][1])
+        if ran[u]:
+            np.testing.assert_allclose(gu, up[o:o + gu.size], rtol=1e-5)
+            np.testing.assert_allclose(gl, lo[o:o + gl.size], rtol=1e-5, atol=1e-30)
+    offsets, idx, val = res.anomalies(abi.ALG_HW)
+    assert np.array_equal(np.diff(offsets.astype(np.int64)), ref["n_anom"][:, 4])
+    for u in np.flatnonzero(ref["n_anom"][:, 4])[:40]:
+        cur = host.segments(u)[2]
+        sl = slice(int(offsets[u]), int(offsets[u + 1]))
+        assert np.all(np.diff(idx[sl].astype(np.int64)) > 0) and np.array_equal(val[sl], cur[idx[sl]])
+        assert int(idx[sl][0]) == int(ref["first_idx"][u, 4])
+    res.free()
+    b.free()
+
+
 @pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400), (100, 777)])
 def test_model_cache_continuous_mode(ctx, oracle, period, hist):
     """Continuous mode: fit Holt-Winters once, then score successive current windows from the cached
