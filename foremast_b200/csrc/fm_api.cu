@@ -162,30 +162,36 @@ void resolve_params(const fm_params *p, DevParams *d) {
   d->alpha = p->alpha;
   d->beta = p->beta;
   d->gamma = p->gamma;
-  {  // powers of the Holt-Winters level/trend transition matrix (fm_hw.cu): with k = period/32 samples
-     // per lane, hw_lane[l] = A^(k*l) (identity for lane 0) and hw_pow[i] = A^(k*2^i)
+  {  // powers of the Holt-Winters level/trend transition matrix: with k samples per lane,
+     // lane[l] = A^(k*l) (identity for lane 0) and pow[i] = A^(k*2^i) -- once for k_hw (k = period/32), once for
+     // k_hw_tm (k = period / fm_hw_tm_lanes(period)), which also takes the chunk weights A^(k-1-i) g
     const double a = p->alpha, ab = p->alpha * p->beta;
     const double A[4] = {1.0 - a, 1.0 - a, -ab, 1.0 - ab};
     auto mul = [](const double *x, const double *y, double *o) {
       const double r[4] = {x[0] * y[0] + x[1] * y[2], x[0] * y[1] + x[1] * y[3], x[2] * y[0] + x[3] * y[2], x[2] * y[1] + x[3] * y[3]};
       for (int i = 0; i < 4; ++i) o[i] = r[i];
     };
-    const uint32_t k = p->period >= 32 ? p->period / 32 : 1;
-    double Ak[4] = {1.0, 0.0, 0.0, 1.0};
-    for (uint32_t i = 0; i < k; ++i) mul(Ak, A, Ak);
-    double P[4] = {1.0, 0.0, 0.0, 1.0};
-    for (int l = 0; l < 32; ++l) {  // A^(k*l)
-      for (int i = 0; i < 4; ++i) d->hw_lane[4 * l + i] = P[i];
-      mul(P, Ak, P);
-    }
-    double Q[4] = {Ak[0], Ak[1], Ak[2], Ak[3]};
-    for (int i = 0; i < 5; ++i) {   // A^(k*2^i)
-      for (int j = 0; j < 4; ++j) d->hw_pow[4 * i + j] = Q[j];
-      mul(Q, Q, Q);
-    }
+    auto powers = [&](uint32_t k, double *lane, double *pw) {
+      double Ak[4] = {1.0, 0.0, 0.0, 1.0};
+      for (uint32_t i = 0; i < k; ++i) mul(Ak, A, Ak);
+      double P[4] = {1.0, 0.0, 0.0, 1.0};
+      for (int l = 0; l < 32; ++l) {  // A^(k*l)
+        for (int i = 0; i < 4; ++i) lane[4 * l + i] = P[i];
+        mul(P, Ak, P);
+      }
+      double Q[4] = {Ak[0], Ak[1], Ak[2], Ak[3]};
+      for (int i = 0; i < 5; ++i) {   // A^(k*2^i)
+        for (int j = 0; j < 4; ++j) pw[4 * i + j] = Q[j];
+        mul(Q, Q, Q);
+      }
+    };
+    powers(p->period >= 32 ? p->period / 32 : 1, d->hw_lane, d->hw_pow);
+    d->hw_tl = fm_hw_tm_lanes(p->period);
+    d->hw_tk = d->hw_tl ? p->period / d->hw_tl : 1;
+    powers(d->hw_tk, d->hw_tlane, d->hw_tpow);
     double v[2] = {a, ab};  // A^(k-1-i) g for i = k-1 .. 0
     for (int i = 0; i < 64; ++i) d->hw_w[2 * i] = d->hw_w[2 * i + 1] = 0.0;
-    for (int i = (int)std::min<uint32_t>(k, 64u) - 1; i >= 0; --i) {
+    for (int i = (int)std::min<uint32_t>(d->hw_tk, 64u) - 1; i >= 0; --i) {
       d->hw_w[2 * i] = v[0];
       d->hw_w[2 * i + 1] = v[1];
       const double nl = A[0] * v[0] + A[1] * v[1], nb = A[2] * v[0] + A[3] * v[1];

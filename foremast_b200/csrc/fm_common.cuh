@@ -41,10 +41,24 @@ struct DevParams {
   // hw_pow[i] = A^(k*2^i), hw_lane[l] = A^(k*l), row-major
   double hw_pow[5 * 4];
   double hw_lane[32 * 4];
-  // hw_w[2i], hw_w[2i+1] = A^(k-1-i) g, g = (a, ab): what sample i of a k-sample chunk contributes to the
-  // level / trend at the end of the chunk (k_hw_tm's chunk offsets as one dot product per component)
+  // The tensor-memory kernel (fm_hw_tm.cu) cuts a season into hw_tl chunks of hw_tk samples, one chunk per lane
+  // (fm_hw_tm_lanes): its own powers hw_tpow[i] = A^(tk*2^i), hw_tlane[l] = A^(tk*l), and the chunk weights
+  // hw_w[2i], hw_w[2i+1] = A^(tk-1-i) g, g = (a, ab): what sample i of a chunk contributes to the level / trend
+  // at the end of the chunk (the chunk offsets as one dot product per component).
+  uint32_t hw_tk, hw_tl;
+  double hw_tpow[5 * 4];
+  double hw_tlane[32 * 4];
   double hw_w[2 * 64];
 };
+
+// Lanes the tensor-memory Holt-Winters kernel uses for one season: the largest divisor of the period that is at
+// most 32, provided it leaves at most 64 samples per lane and at least half the warp busy; 0 = use k_hw.
+static inline uint32_t fm_hw_tm_lanes(uint32_t period) {
+  if (period < 16 || period > 2048) return 0;
+  for (uint32_t l = 32; l >= 16; --l)
+    if (period % l == 0) return period / l <= 64 ? l : 0;
+  return 0;
+}
 
 __device__ __forceinline__ unsigned fm_lane() { return threadIdx.x & 31u; }
 

@@ -19,8 +19,9 @@
 // fp64 throughout; the scan re-associates the sums, so floats match the sequential oracle to
 // ~1e-15 relative (tested at 1e-5), not bit for bit.
 // Algorithmic bytes per unit: 4*(n_model + n_cur) + 8 + 12 + 32.
-// This kernel serves the periods that are not multiples of 32 (and FOREMAST_GPU_HW_SMEM=1, for
-// tests); the others go to fm_hw_tm.cu, which keeps the seasonals in tensor memory.  The per-unit
+// This kernel serves the periods that cannot be cut into 16..32 equal chunks of at most 64 samples
+// (fm_hw_tm_lanes; and FOREMAST_GPU_HW_SMEM=1, for tests); the others go to fm_hw_tm.cu, which keeps the
+// seasonals in tensor memory.  The per-unit
 // gate, the scan and the result bookkeeping are shared (fm_hw_common.cuh).
 #include <cstdlib>
 
@@ -278,7 +279,7 @@ static cudaError_t launch_hw(const DevBatch &b, const DevParams *dp, uint32_t pe
                              uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                              const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, int sm_count,
                              cudaStream_t st, double *state = nullptr) {
-  if (fm_hw_tm_supported(period) && !getenv("FOREMAST_GPU_HW_SMEM"))  // seasonals in tensor memory: 18 units per SM instead of 12
+  if (fm_hw_tm_supported(period) && !getenv("FOREMAST_GPU_HW_SMEM"))  // seasonals in tensor memory: 20 units per SM instead of 12
     return fm_launch_hw_tm(MODE, b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx,
                            emit_val, state, sm_count, st);
   uint64_t blocks = (b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock;

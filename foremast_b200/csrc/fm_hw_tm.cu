@@ -4,7 +4,7 @@
 // reference citations and the maths); what changes is where the period-long seasonal array lives.
 // k_hw keeps it in shared memory, 8 B x period per unit (11.25 KB at period 1440), and that is what
 // caps it at 12 warps per SM -- the kernel is latency-bound, so occupancy is its speed.  Here a
-// super-tile is exactly one season (32*k samples, k = period/32), so lane `l` meets the SAME k
+// super-tile is exactly one season (L chunks of k samples, one per lane), so lane `l` meets the SAME k
 // seasonal slots in every super-tile: the array is lane-private, and Blackwell's tensor memory
 // (256 KB per SM: 128 lanes x 512 32-bit columns, each thread of a warp reaching the columns of its
 // own lane with tcgen05.ld/st.32x32b) holds it as plain scratch -- no tensor-core instruction is
@@ -20,7 +20,9 @@
 // weights (DevParams::hw_w), pass 2 is the plain one-step recurrence.  The super-tile the model window
 // ends in, the current samples and ragged ends take the guarded form, where a current sample whose
 // error is provably inside the band skips the band arithmetic.
-// Used when period % 32 == 0; other periods take k_hw.
+// A season is cut into L chunks of k samples, L the largest divisor of the period up to 32 (fm_hw_tm_lanes: 1440 = 32 x 45,
+// 1000 = 25 x 40, 168 = 28 x 6); lanes past L ride along on lane 0's samples and nothing they compute is kept.
+// Periods without such a divisor (k > 64 or fewer than 16 lanes) take k_hw.
 #include <algorithm>
 
 #include "fm_hw_common.cuh"
@@ -132,13 +134,15 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
                                                              uint32_t *__restrict__ emit_idx, float *__restrict__ emit_val,
                                                              double *__restrict__ state) {
   constexpr bool BANDS = MODE == 1, EMIT = MODE == 2, FIT = MODE == 3, RESUME = MODE == 4;
-  extern __shared__ float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
+  extern __shared__ __align__(16) float s_x[];  // [warps][2][period] fp32 samples: the season being scored and the next one in flight
   __shared__ uint32_t s_tm_base;
   __shared__ double s_apow[5 * 4];    // A^(k*2^i), i = 0..4
   __shared__ double2 s_w[64];         // chunk weights (DevParams::hw_w)
   __shared__ __align__(8) uint64_t s_bar[kMaxWarps][2];  // one mbarrier per warp per sample buffer
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-  const uint32_t m = dp->period, k = m / 32;
+  const uint32_t m = dp->period, k = dp->hw_tk, nl = dp->hw_tl;  // a season = nl chunks of k samples, one per lane
+  const bool busy = lane < nl;         // lanes past the season's chunks ride along on lane 0's samples; nothing they compute is kept
+  const uint32_t bw = (m + 3u) & ~3u;  // words per sample buffer (keeps the second buffer 16 B aligned)
   const uint32_t kq = (k + 3) / 4;  // blocks of four seasonals per lane
   const uint32_t npair = min(k / 8, (kq - 1) / 2);  // leading pairs of whole blocks that have a block after them
 
@@ -150,7 +154,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
                  "n"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
   }
-  if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_pow[threadIdx.x];
+  if (threadIdx.x < 20) s_apow[threadIdx.x] = dp->hw_tpow[threadIdx.x];
   if (threadIdx.x < 64) s_w[threadIdx.x] = make_double2(dp->hw_w[2 * threadIdx.x], dp->hw_w[2 * threadIdx.x + 1]);
   const uint32_t bar_s = keep((uint32_t)__cvta_generic_to_shared(&s_bar[warp][0]));  // buffer 1's barrier: + 8
   if (lane == 0) {
@@ -165,9 +169,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   const uint32_t tS = keep(tm_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * 16u * ((k + 7) / 8));
 
   const double alpha = dp->alpha, ab = dp->alpha * dp->beta, g1 = dp->gamma * (1.0 - dp->alpha);
-  const uint32_t p0 = lane * k;  // this lane's chunk inside a season-long super-tile
-  const uint32_t buf_bytes = m * 4u;
-  const uint32_t xb_s = keep((uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * 2 * m));  // this warp's two buffers
+  const uint32_t p0 = busy ? lane * k : 0u;  // this lane's chunk inside a season-long super-tile
+  const uint32_t buf_bytes = bw * 4u;
+  const uint32_t xb_s = keep((uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * 2 * bw));  // this warp's two buffers
   const uint32_t xs0 = keep(xb_s + 4u * p0);                                                     // this lane's chunk in buffer 0
   const uint32_t ws0 = keep((uint32_t)__cvta_generic_to_shared(s_w));
   uint32_t pb = 0;  // bits 0-1: mbarrier phase to wait for next, per sample buffer; bits 2-3: buffer filled by a bulk copy
@@ -231,7 +235,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
             if ((uint32_t)j < rem) s0 += (double)x[j];
         }
       }
-      s0 += s1;
+      s0 = busy ? s0 + s1 : 0.0;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) s0 += __shfl_xor_sync(0xffffffffu, s0, o);
       return s0;
@@ -303,7 +307,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         }
       }
       const uint32_t qa = q0 + p0;                                      // stream position of the chunk
-      const uint32_t kv = qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
+      const uint32_t kv = busy && qa < n_stream ? min(k, n_stream - qa) : 0u;  // real samples in this lane's chunk
       const uint32_t xs = keep(xs0 + (cur ? buf_bytes : 0u));          // the chunk's samples (shared-window address)
       const bool whole = !RESUME && q0 + m <= ns;  // a whole season of the model window (warp-uniform)
       uint32_t ra[8], rb[8];
@@ -374,14 +378,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         uo.b = ub0 + ub1;
       }
       // ---- the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
-      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, dp->hw_lane + 4 * lane, lane);
+      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, dp->hw_tlane + 4 * lane, lane);
 
       // ---- pass 2: the real recurrence over the chunk
       double l = vin.l, bb = vin.b;
       unsigned long long fmask = 0ull;  // flags of the chunk's current samples (k <= 64)
       const bool tile_has_cur = q0 + m > ns;
       if (!sigma_ready && q0 >= ns) {  // the model window ended with the previous super-tile: close the residual sum
-        double t = sse;
+        double t = busy ? sse : 0.0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         sigma = sqrt(t / (double)(ns - m));
@@ -479,7 +483,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           if (sweep == 1) {
             if (!tile_has_cur) break;
             if (!sigma_ready) {  // the model window ends in this super-tile: close the residual sum first
-              double t = sse;
+              double t = busy ? sse : 0.0;
 #pragma unroll
               for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
               sigma = sqrt(t / (double)(ns - m));
@@ -533,18 +537,18 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       // sample of this super-tile, which lives in lane (nv-1)/k
       {
         const uint32_t nv = min(m, n_stream - q0);
-        const int src = whole ? 31 : (int)((nv - 1) / k);
+        const int src = whole ? (int)nl - 1 : (int)((nv - 1) / k);
         carry.l = __shfl_sync(0xffffffffu, l, src);
         carry.b = __shfl_sync(0xffffffffu, bb, src);
       }
       if (tile_has_cur) {
-        const float *const xp = s_x + (size_t)warp * 2 * m + cur * m + p0;
+        const float *const xp = s_x + (size_t)warp * 2 * bw + cur * bw + p0;
         fm_hw::tile_flags<EMIT>(fmask, lane, qa, ns, w.emit_base, emit_idx, emit_val, xp, n_anom, first);
       }
     }
     if (FIT || RESUME) {  // save the model: state after the last sample, residual sigma, phase, seasonals
       if (FIT && !sigma_ready) {
-        double t = sse;
+        double t = busy ? sse : 0.0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         sigma = sqrt(t / (double)(ns - m));
@@ -556,7 +560,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         tm_ld4(tS + 8 * blk, s);
 #pragma unroll
         for (int j = 0; j < 4; ++j, ++slot)
-          if (4 * blk + j < k) ust[4 + (slot >= m ? slot - m : slot)] = s[j];
+          if (4 * blk + j < k && busy) ust[4 + (slot >= m ? slot - m : slot)] = s[j];
       }
       if (lane == 0) fm_hw::save_state_scalars(ust, carry, sigma, phase, n_stream, m);
       __syncwarp();
@@ -575,17 +579,19 @@ cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, f
                       uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                       const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state, int sm_count,
                       cudaStream_t st) {
-  const uint32_t k = period / 32, kb = (k + 7) / 8;
+  const uint32_t nl = fm_hw_tm_lanes(period);
+  if (!nl) return cudaErrorInvalidValue;
+  const uint32_t k = period / nl, kb = (k + 7) / 8, bw = (period + 3u) & ~3u;
   // warps per CTA: four lane quarters x as many 16*kb-column ranges as fit in 512 columns, capped by
   // the launch bound and by the fp32 season each warp keeps in shared memory
   int warps = (int)std::min<uint32_t>(4 * (512 / (16 * kb)), kMaxWarps);
-  warps = std::min(warps, (227 * 1024 - 1536 - 32) / ((int)period * 8));  // 1.5 KB: the kernel's static shared memory
+  warps = std::min(warps, (227 * 1024 - 1536 - 32) / ((int)bw * 8));  // 1.5 KB: the kernel's static shared memory
   if (warps < 1) return cudaErrorInvalidValue;
   uint64_t blocks = (b.n_units + warps - 1) / warps;
   const uint64_t cap = (uint64_t)sm_count;  // persistent: one CTA is resident per SM (it owns the tensor memory)
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  const int smem = warps * 2 * (int)period * (int)sizeof(float) + 32;  // lds4 may read up to 3 samples past a chunk
+  const int smem = warps * 2 * (int)bw * (int)sizeof(float) + 32;  // lds4 may read up to 3 samples past a chunk
   cudaError_t e = cudaFuncSetAttribute(k_hw_tm<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   k_hw_tm<MODE><<<(unsigned)blocks, warps * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
@@ -595,7 +601,7 @@ cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, f
 
 }  // namespace
 
-bool fm_hw_tm_supported(uint32_t period) { return period >= 32 && period % 32 == 0 && period <= 2048; }
+bool fm_hw_tm_supported(uint32_t period) { return fm_hw_tm_lanes(period) != 0; }
 
 cudaError_t fm_launch_hw_tm(int mode, const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
                             uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,

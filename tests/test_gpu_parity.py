@@ -225,12 +225,15 @@ def test_holt_winters(ctx, oracle, shape, period, n, seasonals, monkeypatch):
 
 @pytest.mark.parametrize("period,shape", [(256, (1041, 0, 133)), (384, (1553, 0, 200)), (512, (2065, 7, 600)),
                                           (1024, (4113, 0, 40)), (1440, (4320, 0, 1440)), (1440, (5000, 0, 3000)),
-                                          (64, (300, 0, 1)), (2048, (6200, 0, 2100))])
+                                          (64, (300, 0, 1)), (2048, (6200, 0, 2100)),
+                                          (168, (1100, 0, 200)), (100, (777, 0, 33)), (1000, (4100, 0, 1300)),
+                                          (34, (180, 0, 40)), (1530, (5000, 0, 100)), (62, (400, 0, 77))])
 def test_holt_winters_tile_classes(ctx, oracle, period, shape):
     """k_hw_tm takes different paths for a whole season of the model window, for the super-tile the model
     window ends in, for whole and ragged super-tiles of current samples and for the last super-tile of a
     unit, and its blocks of four seasonals end differently for every chunk length (period / 32 = 8, 12,
-    16, 32, 45, 2, 64 here).  Scores, bands and the anomaly list against the oracle on each."""
+    16, 32, 45, 2, 64 here; then periods that are k x L with L < 32 lanes: 168 = 6 x 28, 100 = 4 x 25,
+    1000 = 40 x 25, 34 = 2 x 17, 1530 = 51 x 30, 62 = 2 x 31).  Scores, bands and the anomaly list against the oracle on each."""
     n = 120
     b = ctx.batch_synth(n, *shape, flags=abi.SYNTH_RAGGED | abi.SYNTH_ANOMALIES, seed=period + shape[2])
     p = full_params(oracle, abi.ALG_HW, abi.PW_NONE)
