@@ -85,8 +85,13 @@ __device__ __forceinline__ uint32_t keep(uint32_t v) {
 #define FM_LDS_F32(dst, addr, imm) asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(dst) : "r"(addr), "n"(imm))
 #define FM_LDS_V2F64(dst, addr, imm) \
   asm volatile("ld.shared.v2.f64 {%0,%1}, [%2+%3];" : "=d"((dst).x), "=d"((dst).y) : "r"(addr), "n"(imm))
+template <bool VEC>  // VEC: the address is 16 B aligned (chunk lengths that are multiples of four)
 __device__ __forceinline__ void lds4(uint32_t a, float (&x)[4]) {
-  FM_LDS_F32(x[0], a, 0); FM_LDS_F32(x[1], a, 4); FM_LDS_F32(x[2], a, 8); FM_LDS_F32(x[3], a, 12);
+  if constexpr (VEC) {
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "r"(a));
+  } else {
+    FM_LDS_F32(x[0], a, 0); FM_LDS_F32(x[1], a, 4); FM_LDS_F32(x[2], a, 8); FM_LDS_F32(x[3], a, 12);
+  }
 }
 __device__ __forceinline__ void ldw4(uint32_t a, double2 (&w)[4]) {
   FM_LDS_V2F64(w[0], a, 0); FM_LDS_V2F64(w[1], a, 16); FM_LDS_V2F64(w[2], a, 32); FM_LDS_V2F64(w[3], a, 48);
@@ -98,9 +103,11 @@ __device__ __forceinline__ void ldw4(uint32_t a, double2 (&w)[4]) {
 __device__ __forceinline__ void mbar_init(uint32_t bar) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void bulk_load(uint32_t dst, const float *src, uint32_t bytes, uint32_t bar) {
-  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // earlier generic reads of dst come first
+__device__ __forceinline__ void bulk_expect(uint32_t bar, uint32_t bytes) {  // one arrival, `bytes` to come
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy(uint32_t dst, const float *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // earlier generic reads of dst come first
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
@@ -124,7 +131,11 @@ __device__ __forceinline__ void cp_async4_s(uint32_t dst, const void *gmem) {
 
 // MODE as in fm_hw.cu: 0 score, 1 score + bands, 2 emit pass of the anomaly list, 3 fit (model
 // window only, state saved), 4 resume (score the current segment from the saved state, advance it).
-template <int MODE>
+// VEC: the chunk length is a multiple of four.  A lane's chunk then starts 16 B aligned and is read with 128-bit
+// loads; when it is a multiple of eight as well, the chunks are laid out four words apart (stride k + 4), because at a
+// stride of k words with k % 8 == 0 the lanes of a quarter warp would all read the same banks (period 1024: one bank
+// for the whole warp).  Each lane then brings its own chunk in with its own bulk copy.
+template <int MODE, bool VEC>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const DevParams *__restrict__ dp,
                                                              fm_series_score *__restrict__ scores,
                                                              uint32_t *__restrict__ unit_status,
@@ -142,7 +153,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
   const uint32_t m = dp->period, k = dp->hw_tk, nl = dp->hw_tl;  // a season = nl chunks of k samples, one per lane
   const bool busy = lane < nl;         // lanes past the season's chunks ride along on lane 0's samples; nothing they compute is kept
-  const uint32_t bw = (m + 3u) & ~3u;  // words per sample buffer (keeps the second buffer 16 B aligned)
+  const uint32_t cs = VEC && (k & 7u) == 0 ? k + 4u : k;      // chunk stride in shared memory, words
+  const uint32_t bw = ((cs == k ? m : nl * cs) + 3u) & ~3u;  // words per sample buffer (keeps the second buffer 16 B aligned)
   const uint32_t kq = (k + 3) / 4;  // blocks of four seasonals per lane
   const uint32_t npair = min(k / 8, (kq - 1) / 2);  // leading pairs of whole blocks that have a block after them
 
@@ -172,7 +184,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   const uint32_t p0 = busy ? lane * k : 0u;  // this lane's chunk inside a season-long super-tile
   const uint32_t buf_bytes = bw * 4u;
   const uint32_t xb_s = keep((uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * 2 * bw));  // this warp's two buffers
-  const uint32_t xs0 = keep(xb_s + 4u * p0);                                                     // this lane's chunk in buffer 0
+  const uint32_t pw = busy ? lane * cs : 0u;  // ... and where it lies in a sample buffer
+  const uint32_t xs0 = keep(xb_s + 4u * pw);  // this lane's chunk in buffer 0
   const uint32_t ws0 = keep((uint32_t)__cvta_generic_to_shared(s_w));
   uint32_t pb = 0;  // bits 0-1: mbarrier phase to wait for next, per sample buffer; bits 2-3: buffer filled by a bulk copy
 
@@ -190,33 +203,57 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     // size are 16 B aligned (the usual case: model window = history, whole seasons), else 4-byte
     // async copies, all in flight together.  Completion is awaited later (wait_buf).
     auto stage = [&](uint32_t q0s, uint32_t buf) {
-      const uint32_t dst = xb_s + (buf ? buf_bytes : 0u);
+      const uint32_t dst = xb_s + (buf ? buf_bytes : 0u), bar = bar_s + 8u * buf;
       const uint32_t nv = min(m, n_stream - q0s);
-      if (q0s + nv <= ns || q0s >= ns) {  // one segment: one contiguous source
-        const float *src = unit + (q0s < ns ? a0 + q0s : c0 + (q0s - ns));
-        if (((reinterpret_cast<uintptr_t>(src) & 15u) | (nv & 3u)) == 0) {
-          if (lane == 0) bulk_load(dst, src, nv * 4u, bar_s + 8u * buf);
+      const bool one_seg = q0s + nv <= ns || q0s >= ns;  // one contiguous source
+      const float *const src = unit + (q0s < ns ? a0 + q0s : c0 + (q0s - ns));
+      pb &= ~(4u << buf);
+      if (cs == k) {  // chunks back to back: the season lies in shared memory as it does in the stream
+        if (one_seg && ((reinterpret_cast<uintptr_t>(src) & 15u) | (nv & 3u)) == 0) {
+          if (lane == 0) {
+            bulk_expect(bar, nv * 4u);
+            bulk_copy(dst, src, nv * 4u, bar);
+          }
           pb |= 4u << buf;
           return;
         }
+        if (one_seg) {
 #pragma unroll 3
-        for (uint32_t i = lane; i < nv; i += 32) cp_async4_s(dst + 4u * i, src + i);
-      } else {
-        for (uint32_t i = lane; i < nv; i += 32) {
-          const uint32_t q = q0s + i;
-          cp_async4_s(dst + 4u * i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          for (uint32_t i = lane; i < nv; i += 32) cp_async4_s(dst + 4u * i, src + i);
+        } else {
+          for (uint32_t i = lane; i < nv; i += 32) {
+            const uint32_t q = q0s + i;
+            cp_async4_s(dst + 4u * i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          }
+        }
+      } else {  // padded chunks: every lane fetches its own (k * 4 bytes is a multiple of 32)
+        const uint32_t first = lane * k, dl = dst + 4u * pw;
+        const uint32_t cnt = busy && first < nv ? min(k, nv - first) : 0u;  // this lane's samples in the super-tile
+        if (one_seg && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+          const uint32_t nfull = nv / k;  // lanes whose chunk is whole: bulk copies; the ragged one after them: 4-byte copies
+          if (nfull) {
+            if (lane == 0) bulk_expect(bar, nfull * k * 4u);
+            __syncwarp();
+            if (lane < nfull) bulk_copy(dl, src + first, k * 4u, bar);
+            pb |= 4u << buf;
+          }
+          if (lane == nfull)
+            for (uint32_t i = 0; i < cnt; ++i) cp_async4_s(dl + 4u * i, src + first + i);
+        } else {
+          for (uint32_t i = 0; i < cnt; ++i) {
+            const uint32_t q = q0s + first + i;
+            cp_async4_s(dl + 4u * i, unit + (q < ns ? a0 + q : c0 + (q - ns)));
+          }
         }
       }
       cp_async_commit();
-      pb &= ~(4u << buf);
     };
     auto wait_buf = [&](uint32_t buf) {
       if (pb & (4u << buf)) {
         mbar_wait(bar_s + 8u * buf, (pb >> buf) & 1u);
         pb ^= 1u << buf;
-      } else {
-        cp_async_wait<0>();
       }
+      cp_async_wait<0>();
       __syncwarp();
     };
     // sum over the season of the lane's k samples at shared address xa (two accumulators per lane)
@@ -225,7 +262,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
 #pragma unroll 1
       for (uint32_t blk = 0; blk < kq; ++blk, xa += 16u) {
         float x[4];
-        lds4(xa, x);
+        lds4<VEC>(xa, x);
         const uint32_t rem = k - 4 * blk;  // warp-uniform
         if (rem >= 4) {
           s0 += (double)x[0]; s1 += (double)x[1]; s0 += (double)x[2]; s1 += (double)x[3];
@@ -275,7 +312,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
 #pragma unroll 1
         for (uint32_t blk = 0; blk < kq; ++blk, xa += 16u) {
           float x[4];
-          lds4(xa, x);
+          lds4<VEC>(xa, x);
           double s[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) s[j] = 4 * blk + j < k ? (double)x[j] - L0 : 0.0;
@@ -325,7 +362,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         auto p1 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
           float x[4];
           double2 wv[4];
-          lds4(xs + 16u * blk, x);
+          lds4<VEC>(xs + 16u * blk, x);
           ldw4(ws0 + 64u * blk, wv);
           tm_ld_arrive(c);
           if (blk + 1 < kq) tm_ld_issue(tS + 8 * (blk + 1), n);
@@ -352,7 +389,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         auto p1w = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
           float x[4];
           double2 wv[4];
-          lds4(xs + 16u * blk, x);
+          lds4<VEC>(xs + 16u * blk, x);
           ldw4(ws0 + 64u * blk, wv);
           tm_ld_arrive(c);
           tm_ld_issue(tS + 8 * (blk + 1), n);
@@ -403,7 +440,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         };
         auto p2 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
           float x[4];
-          lds4(xs + 16u * blk, x);
+          lds4<VEC>(xs + 16u * blk, x);
           tm_ld_arrive(c);
           if (blk + 1 < kq) tm_ld_issue(tS + 8 * (blk + 1), n);
           const uint32_t rem = k - 4u * blk;
@@ -419,7 +456,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         };
         auto p2w = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
           float x[4];
-          lds4(xs + 16u * blk, x);
+          lds4<VEC>(xs + 16u * blk, x);
           tm_ld_arrive(c);
           tm_ld_issue(tS + 8 * (blk + 1), n);
 #pragma unroll
@@ -449,7 +486,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         for (uint32_t blk = 0; 4 * blk < kmax; ++blk) {
           float xf[4];
           double s[4];
-          lds4(xs + 16u * blk, xf);
+          lds4<VEC>(xs + 16u * blk, xf);
           tm_ld4(tS + 8 * blk, s);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -497,7 +534,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
             if (__all_sync(0xffffffffu, 4 * blk >= hi || 4 * blk + 4 <= lo)) continue;  // no lane has work in this block
             float xf[4];
             double s[4];
-            lds4(xs + 16u * blk, xf);
+            lds4<VEC>(xs + 16u * blk, xf);
             tm_ld4(tS + 8 * blk, s);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -542,7 +579,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         carry.b = __shfl_sync(0xffffffffu, bb, src);
       }
       if (tile_has_cur) {
-        const float *const xp = s_x + (size_t)warp * 2 * bw + cur * bw + p0;
+        const float *const xp = s_x + (size_t)warp * 2 * bw + cur * bw + pw;
         fm_hw::tile_flags<EMIT>(fmask, lane, qa, ns, w.emit_base, emit_idx, emit_val, xp, n_anom, first);
       }
     }
@@ -574,16 +611,17 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tm_base), "n"(512));
 }
 
-template <int MODE>
-cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
-                      uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
-                      const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state, int sm_count,
-                      cudaStream_t st) {
+template <int MODE, bool VEC>
+cudaError_t launch_tm2(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                       uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                       const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state, int sm_count,
+                       cudaStream_t st) {
   const uint32_t nl = fm_hw_tm_lanes(period);
   if (!nl) return cudaErrorInvalidValue;
-  const uint32_t k = period / nl, kb = (k + 7) / 8, bw = (period + 3u) & ~3u;
+  const uint32_t k = period / nl, kb = (k + 7) / 8;
+  const uint32_t cs = VEC && (k & 7u) == 0 ? k + 4u : k, bw = ((cs == k ? period : nl * cs) + 3u) & ~3u;  // as in the kernel
   // warps per CTA: four lane quarters x as many 16*kb-column ranges as fit in 512 columns, capped by
-  // the launch bound and by the fp32 season each warp keeps in shared memory
+  // the launch bound and by the two fp32 seasons each warp keeps in shared memory
   int warps = (int)std::min<uint32_t>(4 * (512 / (16 * kb)), kMaxWarps);
   warps = std::min(warps, (227 * 1024 - 1536 - 32) / ((int)bw * 8));  // 1.5 KB: the kernel's static shared memory
   if (warps < 1) return cudaErrorInvalidValue;
@@ -591,12 +629,25 @@ cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, f
   const uint64_t cap = (uint64_t)sm_count;  // persistent: one CTA is resident per SM (it owns the tensor memory)
   if (blocks > cap) blocks = cap;
   if (blocks == 0) return cudaSuccess;
-  const int smem = warps * 2 * (int)bw * (int)sizeof(float) + 32;  // lds4 may read up to 3 samples past a chunk
-  cudaError_t e = cudaFuncSetAttribute(k_hw_tm<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int smem = warps * 2 * (int)bw * (int)sizeof(float) + 32;  // scalar lds4 may read up to 3 samples past a chunk
+  cudaError_t e = cudaFuncSetAttribute(k_hw_tm<MODE, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  k_hw_tm<MODE><<<(unsigned)blocks, warps * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
-                                                           emit_off, emit_idx, emit_val, state);
+  k_hw_tm<MODE, VEC><<<(unsigned)blocks, warps * 32, smem, st>>>(b, dp, scores, unit_status, unit_points, band_up, band_lo,
+                                                                emit_off, emit_idx, emit_val, state);
   return cudaGetLastError();
+}
+
+template <int MODE>
+cudaError_t launch_tm(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
+                      uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
+                      const unsigned long long *emit_off, uint32_t *emit_idx, float *emit_val, double *state, int sm_count,
+                      cudaStream_t st) {
+  const uint32_t nl = fm_hw_tm_lanes(period);
+  if (nl && (period / nl) % 4 == 0)
+    return launch_tm2<MODE, true>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx,
+                                  emit_val, state, sm_count, st);
+  return launch_tm2<MODE, false>(b, dp, period, scores, unit_status, unit_points, band_up, band_lo, emit_off, emit_idx,
+                                 emit_val, state, sm_count, st);
 }
 
 }  // namespace
