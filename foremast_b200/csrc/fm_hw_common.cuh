@@ -93,6 +93,7 @@ __device__ __forceinline__ bool unit_begin(const DevBatch &b, const DevParams *_
 // State entering each lane's chunk: inclusive warp scan of the chunk maps v -> A^k v + u with the
 // precomputed A^(k*2^i) (apow), shifted one lane, plus the carry of the previous super-tile
 // through A^(k*lane) (alane).
+template <bool CARRY = true>  // false: the super-tile starts from a zero state (carry and alane are not read)
 __device__ __forceinline__ V2 scan_chunks(V2 uo, V2 carry, const double *apow, const double *alane, unsigned lane) {
   V2 inc = uo;
 #pragma unroll
@@ -111,9 +112,11 @@ __device__ __forceinline__ V2 scan_chunks(V2 uo, V2 carry, const double *apow, c
   vin.l = __shfl_up_sync(0xffffffffu, inc.l, 1);
   vin.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
   if (lane == 0) { vin.l = 0.0; vin.b = 0.0; }
-  const V2 cv = matvec(alane, carry);
-  vin.l += cv.l;
-  vin.b += cv.b;
+  if (CARRY) {
+    const V2 cv = matvec(alane, carry);
+    vin.l += cv.l;
+    vin.b += cv.b;
+  }
   return vin;
 }
 

@@ -354,9 +354,17 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
       //      is enough: an offset is only ever used by the lanes after it, and the one chunk of a super-tile
       //      that can be short is the last one with samples (whatever this computes there, and in the empty
       //      chunks behind it, only reaches lanes that have no samples).  Skipped when one lane holds it all.
+      //      The offsets are those of a DEVIATION: with (r_l, r_b) the carried state, the state is written as
+      //      (r_l, 0) + r_b A^i e_2 + d_i -- the first term is a fixed point of the recurrence under the constant
+      //      input r_l, the second the free motion of the carried trend, and d obeys the same recurrence with
+      //      inputs y_i - r_l from d_0 = 0.  So the scan needs no carry term, what it adds up is small next to the
+      //      level, and a constant series (deviation exactly zero) comes out exactly as in the sequential form
+      //      (with the carry pushed through powers of A it came out with 1e-16 of noise per super-tile, which a
+      //      marginally stable parameter set amplified past the 1e-9 guard of the flags).
       V2 uo;
       uo.l = 0.0;
       uo.b = 0.0;
+      const double r_l = carry.l, r_b = carry.b;
       if (min(m, n_stream - q0) > k) {
         double ul0 = 0.0, ub0 = 0.0, ul1 = 0.0, ub1 = 0.0;
         auto p1 = [&](uint32_t blk, uint32_t (&c)[8], uint32_t (&n)[8]) {
@@ -368,8 +376,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           if (blk + 1 < kq) tm_ld_issue(tS + 8 * (blk + 1), n);
           const uint32_t rem = k - 4u * blk;  // warp-uniform
           if (rem >= 4) {
-            const double y0 = (double)x[0] - tm_get(c, 0), y1 = (double)x[1] - tm_get(c, 1);
-            const double y2 = (double)x[2] - tm_get(c, 2), y3 = (double)x[3] - tm_get(c, 3);
+            const double y0 = ((double)x[0] - tm_get(c, 0)) - r_l, y1 = ((double)x[1] - tm_get(c, 1)) - r_l;
+            const double y2 = ((double)x[2] - tm_get(c, 2)) - r_l, y3 = ((double)x[3] - tm_get(c, 3)) - r_l;
             ul0 = fma(wv[0].x, y0, ul0); ub0 = fma(wv[0].y, y0, ub0);
             ul1 = fma(wv[1].x, y1, ul1); ub1 = fma(wv[1].y, y1, ub1);
             ul0 = fma(wv[2].x, y2, ul0); ub0 = fma(wv[2].y, y2, ub0);
@@ -378,7 +386,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
               if ((uint32_t)j < rem) {
-                const double y = (double)x[j] - tm_get(c, j);
+                const double y = ((double)x[j] - tm_get(c, j)) - r_l;
                 ul0 = fma(wv[j].x, y, ul0);
                 ub0 = fma(wv[j].y, y, ub0);
               }
@@ -393,8 +401,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
           ldw4(ws0 + 64u * blk, wv);
           tm_ld_arrive(c);
           tm_ld_issue(tS + 8 * (blk + 1), n);
-          const double y0 = (double)x[0] - tm_get(c, 0), y1 = (double)x[1] - tm_get(c, 1);
-          const double y2 = (double)x[2] - tm_get(c, 2), y3 = (double)x[3] - tm_get(c, 3);
+          const double y0 = ((double)x[0] - tm_get(c, 0)) - r_l, y1 = ((double)x[1] - tm_get(c, 1)) - r_l;
+          const double y2 = ((double)x[2] - tm_get(c, 2)) - r_l, y3 = ((double)x[3] - tm_get(c, 3)) - r_l;
           ul0 = fma(wv[0].x, y0, ul0); ub0 = fma(wv[0].y, y0, ub0);
           ul1 = fma(wv[1].x, y1, ul1); ub1 = fma(wv[1].y, y1, ub1);
           ul0 = fma(wv[2].x, y2, ul0); ub0 = fma(wv[2].y, y2, ub0);
@@ -415,10 +423,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         uo.b = ub0 + ub1;
       }
       // ---- the state entering this lane's chunk: warp scan of the chunk maps v -> A^k v + u
-      const V2 vin = fm_hw::scan_chunks(uo, carry, s_apow, dp->hw_tlane + 4 * lane, lane);
+      const V2 vin = fm_hw::scan_chunks<false>(uo, carry, s_apow, nullptr, lane);
 
-      // ---- pass 2: the real recurrence over the chunk
-      double l = vin.l, bb = vin.b;
+      // ---- pass 2: the real recurrence over the chunk, from (r_l, 0) + r_b A^p0 e_2 + the deviation
+      double l = r_l + fma(r_b, dp->hw_tlane[4 * lane + 1], vin.l), bb = fma(r_b, dp->hw_tlane[4 * lane + 3], vin.b);
       unsigned long long fmask = 0ull;  // flags of the chunk's current samples (k <= 64)
       const bool tile_has_cur = q0 + m > ns;
       if (!sigma_ready && q0 >= ns) {  // the model window ended with the previous super-tile: close the residual sum
