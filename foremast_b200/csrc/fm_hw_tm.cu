@@ -125,6 +125,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+// shared -> global bulk copy (the model cache's seasonals go out as one 8 * period byte store)
+__device__ __forceinline__ void bulk_store(void *dst, uint32_t src, uint32_t bytes) {
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // the generic writes of src come first
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");  // src may be overwritten from here on
+}
+__device__ __forceinline__ double lds_f64(uint32_t a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
 __device__ __forceinline__ void cp_async4_s(uint32_t dst, const void *gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(gmem) : "memory");
 }
@@ -286,20 +299,36 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
     bool landed = false;
     __syncwarp();        // the previous unit is done with both buffers
     if (RESUME) {
-      stage(0, 0);
+      // The cached seasonals (slot order, 8 * period bytes -- as much as the two sample buffers hold) come in as one
+      // bulk copy (coalesced 8-byte loads when the record is not 16 B aligned); each lane then picks the slots
+      // of its chunk.  Read straight from global, a lane's 8-byte loads are a period / 32 apart from its
+      // neighbours': four times the traffic, and slower than scoring the whole history again.
+      if ((reinterpret_cast<uintptr_t>(ust) & 15u) == 0 && (m & 1u) == 0) {
+        if (lane == 0) {
+          bulk_expect(bar_s, m * 8u);
+          bulk_copy(xb_s, reinterpret_cast<const float *>(ust + 4), m * 8u, bar_s);
+        }
+        pb |= 4u;
+      } else {
+        for (uint32_t i = lane; i < m; i += 32) sts_f64(xb_s + 8u * i, ust[4 + i]);
+        pb &= ~4u;
+      }
       carry.l = ust[0];
       carry.b = ust[1];
       sigma = ust[2];
       sigma_ready = true;
       phase = (uint32_t)ust[3];
+      wait_buf(0);
       uint32_t slot = phase + p0;  // < 2m: phase < m and p0 + i < m
 #pragma unroll 1
       for (uint32_t blk = 0; blk < kq; ++blk) {
         double s[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j, ++slot) s[j] = 4 * blk + j < k ? ust[4 + (slot >= m ? slot - m : slot)] : 0.0;
+        for (int j = 0; j < 4; ++j, ++slot) s[j] = 4 * blk + j < k ? lds_f64(xb_s + 8u * (slot >= m ? slot - m : slot)) : 0.0;
         tm_st4(tS + 8 * blk, s);
       }
+      __syncwarp();  // every lane has its seasonals: the buffers can take samples
+      stage(0, 0);
     } else {
       // ---- initialisation from the first two seasons (D5); both lie inside the model window.  The
       //      second one is also the first super-tile scored below, so it stays where it lands.
@@ -598,6 +627,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         sigma = sqrt(t / (double)(ns - m));
       }
+      // seasonals: into the (now idle) sample buffers in slot order, then out as one bulk store
+      __syncwarp();
       uint32_t slot = phase + p0;
 #pragma unroll 1
       for (uint32_t blk = 0; blk < kq; ++blk) {
@@ -605,7 +636,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_hw_tm(DevBatch b, const D
         tm_ld4(tS + 8 * blk, s);
 #pragma unroll
         for (int j = 0; j < 4; ++j, ++slot)
-          if (4 * blk + j < k && busy) ust[4 + (slot >= m ? slot - m : slot)] = s[j];
+          if (4 * blk + j < k && busy) sts_f64(xb_s + 8u * (slot >= m ? slot - m : slot), s[j]);
+      }
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // every lane's writes before the bulk store reads them
+      __syncwarp();
+      if ((reinterpret_cast<uintptr_t>(ust) & 15u) == 0 && (m & 1u) == 0) {
+        if (lane == 0) bulk_store(ust + 4, xb_s, m * 8u);
+      } else {
+        for (uint32_t i = lane; i < m; i += 32) ust[4 + i] = lds_f64(xb_s + 8u * i);
       }
       if (lane == 0) fm_hw::save_state_scalars(ust, carry, sigma, phase, n_stream, m);
       __syncwarp();
