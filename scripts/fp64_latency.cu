@@ -1,3 +1,6 @@
+// Dependent-issue latency and issue rate of fp64 operations on one SM (B200: a dependent DFMA / DADD issues 8 cycles
+// after its producer, independent ones every 2.2 cycles per scheduler) -- the figures profiles/r2_hw_tm.md reasons with.
+// build + run: nvcc -gencode arch=compute_100a,code=sm_100a -O3 --fmad=false -o /tmp/fp64_latency scripts/fp64_latency.cu && /tmp/fp64_latency
 #include <cstdio>
 #include <cuda_runtime.h>
 __global__ void k(double *out, long long *cyc, double a, double b) {
