@@ -511,7 +511,14 @@ def run_ours(args):
                          "frac_of_spec_8000": kernels[dom]["achieved_gbs"] / 8000.0,
                          "note": ("the rank kernels are bound by instruction issue (a register sorting network of 1504 integer "
                                   "min/max per lane per sort, then shared-memory searches; profiles/r2_rank_mw.md), not by HBM; "
-                                  "the HBM-bound kernels of this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None},
+                                  "the HBM-bound kernels of this path are under \"kernels\" (band_*)") if dom.startswith("rank") else None,
+                         # the bound that does apply to the rank kernels: warp instructions executed per unit (ncu, constant for
+                         # this shape: profiles/r2_rank_mw.md, profiles/r2_step_1M.md) against the issue slots of the launch
+                         "issue": ({"warp_instructions_per_unit": {"rank_mw": 5670, "rank_wilcoxon": 3710}[dom],
+                                    "frac": {"rank_mw": 5670, "rank_wilcoxon": 3710}[dom] * n /
+                                            (148 * 4 * (clocks.get("sm_mhz") or 1965) * 1e6 * kernels[dom]["ms"] * 1e-3),
+                                    "note": "share of the issue slots (148 SMs x 4 schedulers x SM clock) the kernel's instructions fill"}
+                                   if dom in ("rank_mw", "rank_wilcoxon") else None)},
             "kernels": kernels,
             "other_configs": other,
             "parity": parity,
