@@ -88,6 +88,7 @@ struct fm_result {
   DevParams *d_params = nullptr;
   fm_series_score *d_scores = nullptr;
   uint32_t *d_unit_status = nullptr, *d_unit_points = nullptr, *d_counts = nullptr;
+  uint32_t *d_order = nullptr;  // k_band's unit order (fm_launch_band_order); not in the small-job arena
   unsigned long long *d_worst = nullptr;
   fm_verdict *d_verdicts = nullptr;
   float *d_band_up = nullptr, *d_band_lo = nullptr;
@@ -697,10 +698,12 @@ void fm_batch_free(fm_batch *b) {
 
 // ------------------------------------------------------------------ scoring
 
+constexpr uint64_t kMinOrderedUnits = 131072;  // the order costs ~10 us per launch (its kernel + one more dependent launch): not worth it on small batches
+
 static void result_release(fm_result *r) {
   if (!r->ctx) { delete r; return; }
   cudaStream_t st = r->ctx->stream;
-  void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts,
+  void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts, r->d_order,
                   r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo, r->d_anom_off, r->d_anom_idx, r->d_anom_val};
   for (void *p : ptrs)
     if (p) cudaFreeAsync(p, st);
@@ -744,6 +747,8 @@ static int result_alloc(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   FM_R(cudaMallocAsync(&r->d_scores, (n + 1) * sizeof(fm_series_score), st));
   FM_R(cudaMallocAsync(&r->d_unit_status, (n + 1) * sizeof(uint32_t), st));
   FM_R(cudaMallocAsync(&r->d_unit_points, (n + 1) * sizeof(uint32_t), st));
+  static const bool no_order = getenv("FOREMAST_GPU_NO_ORDER") != nullptr;  // A/B switch for scripts/ragged_time.py
+  if (n >= kMinOrderedUnits && !no_order) FM_R(cudaMallocAsync(&r->d_order, (n + 1) * sizeof(uint32_t), st));
   FM_R(cudaMallocAsync(&r->d_counts, (4 * ns + 4) * sizeof(uint32_t), st));
   FM_R(cudaMallocAsync(&r->d_worst, (ns + 1) * sizeof(unsigned long long), st));
   FM_R(cudaMallocAsync(&r->d_verdicts, (ns + 1) * sizeof(fm_verdict), st));
@@ -783,6 +788,10 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
     FM_R(cudaEventRecord(r->ev[2], st));
   if (timed) FM_R(cudaEventRecord(r->ev[3], st));
   const bool band_in_kband = (p->band_algorithm & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES)) != 0;
+  if (r->d_order && i1 - i0 >= kMinOrderedUnits && (p->algorithms & (FM_ALG_MA_ALL | FM_ALG_MA_ROLLING | FM_ALG_EWMA | FM_ALG_DES))) {
+    FM_R(fm_launch_band_order(db, r->d_order + i0, st));  // ragged batches: about equally long units per warp
+    db.order = r->d_order + i0;
+  }
   FM_R(fm_launch_band(db, r->d_params, p->algorithms, do_rank, scores, ustat, upts,
                       band_in_kband ? r->d_band_up : nullptr, band_in_kband ? r->d_band_lo : nullptr, st));
   if (p->algorithms & FM_ALG_HW)

@@ -308,8 +308,13 @@ __device__ __forceinline__ void cur_update(State<ALGS> &s, const Rule &r, double
 // MODE 0: score.  MODE 1: score and materialise the per-point band of dp->band_algorithm.
 // MODE 2: emit pass of the anomaly list -- ALGS is one algorithm, only units with anomalies are
 // read again, and every flagged point is written to (emit_idx, emit_val) at emit_off[u] + k.
+// Two 8-warp blocks per SM need at most 128 registers; the kernels with three or four scorers where ptxas would take a
+// few more (and halve the occupancy) are held to that.  The others are left alone: told "two blocks", ptxas spends the
+// allowance (91 -> 126 registers for EWMA + DES), which costs the 6-warp blocks of small batches their third block.
+constexpr int band_min_blocks(uint32_t algs) { return (algs == 7u || algs == 14u || algs == 15u) ? 2 : 0; }  // 0: no statement
+
 template <uint32_t ALGS, int MODE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const DevParams *__restrict__ dp,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_band(DevBatch b, const DevParams *__restrict__ dp,
                                                               bool rank_ran, fm_series_score *__restrict__ scores,
                                                               uint32_t *__restrict__ unit_status,
                                                               uint32_t *__restrict__ unit_points,
@@ -330,8 +335,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_band(DevBatch b, const 
   int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingB) + warp * 32;
   uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingB + wpb * 32 * 8) + warp * 32;
   float *const s_lo = reinterpret_cast<float *>(smem_raw + kRingB + wpb * 32 * (8 + 4)) + warp * (32 * kRowWords);  // MODE 1 only
-  const uint64_t u = ((uint64_t)blockIdx.x * wpb + warp) * 32 + lane;
-  const bool have = u < b.n_units;
+  const uint64_t gid = ((uint64_t)blockIdx.x * wpb + warp) * 32 + lane;
+  const bool have = gid < b.n_units;
+  const uint64_t u = have && b.order ? (uint64_t)b.order[gid] : gid;  // see fm_launch_band_order
 
   // ---- per-lane unit description
   int64_t off = 0;
@@ -655,7 +661,94 @@ cudaError_t launch(const DevBatch &b, const DevParams *dp, bool rank_ran, fm_ser
   return launch_mode<ALGS, 0>(b, dp, rank_ran, scores, unit_status, unit_points, nullptr, nullptr, nullptr, nullptr, nullptr, st);
 }
 
+// ---- unit order for ragged batches -------------------------------------------------------------------
+// k_band gives a thread a unit and a warp the longest of its 32 units' time; chunks in which the lanes are in
+// different segments take the guarded path.  A batch of jobs with different window lengths therefore ran at
+// half the speed of a uniform batch of the same size (scripts/ragged_time.py).  This kernel groups the units of
+// every tile of 2048 by length -- one block, a counting sort in shared memory over 32 x 32 classes of (total
+// length, current length) in chunks, the classes spread over the range the tile actually has -- and k_band takes
+// unit order[t] instead of unit t.  A tile of equally long units (the usual batch) gets the identity; units
+// stay inside their tile, so the samples a block reads stay close together.  Within a class the order is the
+// order of arrival: which units share a warp may differ from run to run, what is computed for a unit does not.
+constexpr int kOrderTile = 2048;
+
+__global__ void __launch_bounds__(kOrderTile / 2) k_band_order(DevBatch b, uint32_t *__restrict__ order) {
+  __shared__ uint32_t s_bin[1024];   // class sizes, then running positions
+  __shared__ uint32_t s_red[4][32];  // per-warp min / max of the two lengths
+  const uint64_t base = (uint64_t)blockIdx.x * kOrderTile;
+  const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+  uint32_t tc[2], cc[2];  // total and current length in chunks of this thread's two units (t, t + 1024)
+  uint32_t lo_t = 0xFFFFFFFFu, hi_t = 0, lo_c = 0xFFFFFFFFu, hi_c = 0;
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const uint64_t u = base + t + e * (kOrderTile / 2);
+    tc[e] = cc[e] = 0xFFFFFFFFu;
+    if (u < b.n_units) {
+      const uint32_t nc = b.seg_lens[3 * u + 2], tot = b.seg_lens[3 * u] + b.seg_lens[3 * u + 1] + nc;
+      tc[e] = tot / kChunk; cc[e] = nc / kChunk;
+      lo_t = min(lo_t, tc[e]); hi_t = max(hi_t, tc[e]); lo_c = min(lo_c, cc[e]); hi_c = max(hi_c, cc[e]);
+    }
+  }
+  s_bin[t] = 0;
+  lo_t = __reduce_min_sync(0xffffffffu, lo_t); hi_t = __reduce_max_sync(0xffffffffu, hi_t);
+  lo_c = __reduce_min_sync(0xffffffffu, lo_c); hi_c = __reduce_max_sync(0xffffffffu, hi_c);
+  if (lane == 0) { s_red[0][warp] = lo_t; s_red[1][warp] = hi_t; s_red[2][warp] = lo_c; s_red[3][warp] = hi_c; }
+  __syncthreads();
+  lo_t = __reduce_min_sync(0xffffffffu, s_red[0][lane]); hi_t = __reduce_max_sync(0xffffffffu, s_red[1][lane]);
+  lo_c = __reduce_min_sync(0xffffffffu, s_red[2][lane]); hi_c = __reduce_max_sync(0xffffffffu, s_red[3][lane]);
+  if (lo_t >= hi_t && lo_c >= hi_c) {  // equally long units (or none): identity
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const uint64_t u = base + t + e * (kOrderTile / 2);
+      if (u < b.n_units) order[u] = (uint32_t)u;
+    }
+    return;
+  }
+  // 32 classes over [lo, hi] of each length (exact when the range has at most 32 values)
+  const uint32_t st = (hi_t - lo_t) / 32u + 1u, sc = (hi_c - lo_c) / 32u + 1u;
+  uint32_t bin[2];
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    bin[e] = 0xFFFFFFFFu;
+    if (tc[e] != 0xFFFFFFFFu) {
+      bin[e] = ((tc[e] - lo_t) / st) * 32u + (cc[e] - lo_c) / sc;
+      atomicAdd(&s_bin[bin[e]], 1u);
+    }
+  }
+  __syncthreads();
+  {  // exclusive scan of the 1024 class sizes: warp scans, then the warp totals
+    const uint32_t v = s_bin[t];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((int)lane >= o) inc += x;
+    }
+    __syncthreads();
+    if (lane == 31) s_red[0][warp] = inc;
+    __syncthreads();
+    uint32_t w = s_red[0][lane], winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t x = __shfl_up_sync(0xffffffffu, winc, o);
+      if ((int)lane >= o) winc += x;
+    }
+    const uint32_t before = __shfl_sync(0xffffffffu, winc - w, warp);  // units in the warps' classes before this one's
+    s_bin[t] = before + inc - v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int e = 0; e < 2; ++e)
+    if (bin[e] != 0xFFFFFFFFu) order[base + atomicAdd(&s_bin[bin[e]], 1u)] = (uint32_t)(base + t + e * (kOrderTile / 2));
+}
+
 }  // namespace
+
+cudaError_t fm_launch_band_order(const DevBatch &b, uint32_t *order, cudaStream_t st) {
+  if (!b.n_units) return cudaSuccess;
+  k_band_order<<<(unsigned)((b.n_units + kOrderTile - 1) / kOrderTile), kOrderTile / 2, 0, st>>>(b, order);
+  return cudaGetLastError();
+}
 
 // algorithms: subset of {MA_ALL, MA_ROLLING, EWMA, DES}; 0 still runs (it resolves unknown units and statuses).
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,

@@ -22,6 +22,9 @@ struct DevBatch {
   const uint32_t *service_id; // [n_units]
   const uint8_t *metric_type; // [n_units]
   uint64_t first_unit;        // global index of unit 0 (multi-GPU shards)
+  // optional (k_band only): thread t scores unit order[t] -- the units of a tile of 2048 sorted by length, so that the
+  // 32 units of a warp are about equally long when the batch is ragged (fm_launch_band_order)
+  const uint32_t *order = nullptr;
 };
 
 struct DevRule {
@@ -94,6 +97,7 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
                            float *band_up, float *band_lo, cudaStream_t st);
+cudaError_t fm_launch_band_order(const DevBatch &b, uint32_t *order, cudaStream_t st);
 cudaError_t fm_launch_hw(const DevBatch &b, const DevParams *dp, uint32_t period, fm_series_score *scores,
                          uint32_t *unit_status, uint32_t *unit_points, float *band_up, float *band_lo,
                          int sm_count, cudaStream_t st);

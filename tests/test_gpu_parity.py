@@ -262,6 +262,27 @@ def test_holt_winters_tile_classes(ctx, oracle, period, shape):
     b.free()
 
 
+def test_ragged_large_batch_takes_the_ordered_band_path(ctx, oracle):
+    """Batches of 131 072 units and more are scored by k_band in a per-tile order that puts units of similar
+    length into the same warp (fm_launch_band_order).  Every unit here has its own lengths, so no tile gets the
+    identity order; scores and verdicts against the oracle on all of them."""
+    n = 140_000
+    rng = np.random.default_rng(77)
+    nh = rng.choice([0, 0, 0, 40, 100], n)
+    nb, nc = rng.integers(20, 200, n), rng.integers(1, 160, n)
+    tot = nh + nb + nc
+    offs = np.zeros(n + 1, np.int64)
+    np.cumsum(tot + (-tot) % 4, out=offs[1:])
+    vals = (rng.normal(50.0, 5.0, int(offs[-1])) + (rng.random(int(offs[-1])) < 0.002) * 60.0).astype(np.float32)
+    csr = abi.HostCsr(vals, offs, np.stack([nh, nb, nc], axis=1), np.arange(n) // 20, rng.integers(0, 10, n))
+    b = ctx.batch_from_csr(csr)
+    p = full_params(oracle, abi.ALG_MA_ALL | abi.ALG_MA_ROLLING | abi.ALG_EWMA | abi.ALG_DES, abi.PW_MANN_WHITE)
+    p.ma_window = 10
+    got, worst = check_batch(ctx, oracle, b, p)
+    assert (got["n_anom"].sum(axis=0)[:4] > 0).all()
+    b.free()
+
+
 @pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400), (100, 777)])
 def test_model_cache_continuous_mode(ctx, oracle, period, hist):
     """Continuous mode: fit Holt-Winters once, then score successive current windows from the cached
