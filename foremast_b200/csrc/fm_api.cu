@@ -67,6 +67,7 @@ struct fm_batch {
   bool sealed = false, owns = true;
   uint64_t n_units = 0, n_values = 0;  // n_values: allocated elements incl. 32 pad
   uint32_t n_services = 0, max_hist = 0, max_base = 0, max_cur = 0;
+  uint32_t rank_mask_w = 0, rank_mask_m = 0;  // sort-size classes present (fm_rank_class); 0 = not known (one launch for all)
   uint64_t first_unit = 0;
   float *d_values = nullptr;
   int64_t *d_offsets = nullptr;
@@ -89,6 +90,7 @@ struct fm_result {
   fm_series_score *d_scores = nullptr;
   uint32_t *d_unit_status = nullptr, *d_unit_points = nullptr, *d_counts = nullptr;
   uint32_t *d_order = nullptr;  // k_band's unit order (fm_launch_band_order); not in the small-job arena
+  uint32_t *d_rank_classes = nullptr;  // class sizes + unit lists of a batch with several rank sort sizes (fm_launch_rank)
   unsigned long long *d_worst = nullptr;
   fm_verdict *d_verdicts = nullptr;
   float *d_band_up = nullptr, *d_band_lo = nullptr;
@@ -251,7 +253,7 @@ int upload_aligned(fm_batch *b, const fm_csr *h, uint64_t used) {
 // host-side scan of a CSR: validity, alignment, maxima
 int scan_host_csr(fm_ctx *ctx, const fm_csr *h, bool *aligned, uint64_t *used, fm_batch *b) {
   *aligned = true;
-  uint32_t mh = 0, mb = 0, mc = 0, ms = 0;
+  uint32_t mh = 0, mb = 0, mc = 0, ms = 0, kw = 0, km = 0;
   for (uint64_t u = 0; u < h->n_units; ++u) {
     const int64_t o = h->offsets[u], o1 = h->offsets[u + 1];
     const uint64_t len = (uint64_t)h->seg_lens[3 * u] + h->seg_lens[3 * u + 1] + h->seg_lens[3 * u + 2];
@@ -260,8 +262,11 @@ int scan_host_csr(fm_ctx *ctx, const fm_csr *h, bool *aligned, uint64_t *used, f
     mh = std::max(mh, h->seg_lens[3 * u]);
     mb = std::max(mb, h->seg_lens[3 * u + 1]);
     mc = std::max(mc, h->seg_lens[3 * u + 2]);
+    kw |= 1u << fm_rank_class(std::min(h->seg_lens[3 * u + 1], h->seg_lens[3 * u + 2]));
+    km |= 1u << fm_rank_class(std::max(h->seg_lens[3 * u + 1], h->seg_lens[3 * u + 2]));
     if (h->service_id) ms = std::max(ms, h->service_id[u]);
   }
+  b->rank_mask_w = kw; b->rank_mask_m = km;
   *used = h->n_units ? (uint64_t)h->offsets[h->n_units] : 0;
   if (h->n_units && (h->offsets[h->n_units] & 3)) *used = (*used + 3) & ~3ull;
   b->max_hist = mh; b->max_base = mb; b->max_cur = mc;
@@ -602,7 +607,7 @@ int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
   b->d_seg = const_cast<uint32_t *>(d->seg_lens);
   b->d_sid = const_cast<uint32_t *>(d->service_id);
   b->d_mt = const_cast<uint8_t *>(d->metric_type);
-  uint32_t *d_stats = nullptr, h_stats[6] = {0, 0, 0, 0, 0, 0};
+  uint32_t *d_stats = nullptr, h_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   cudaError_t e = cudaMallocAsync(&d_stats, sizeof(h_stats), ctx->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(d_stats, 0, sizeof(h_stats), ctx->stream);
   if (e == cudaSuccess) {
@@ -623,6 +628,7 @@ int fm_batch_from_device(fm_ctx *ctx, const fm_csr *d, fm_batch **out) {
   if (h_stats[4]) { delete b; return set_err(ctx, FM_E_ALIGN, "device CSR offsets must be multiples of 4 elements"); }
   if (h_stats[5]) { delete b; return set_err(ctx, FM_E_INVALID, "device CSR units overlap"); }
   b->max_hist = h_stats[0]; b->max_base = h_stats[1]; b->max_cur = h_stats[2];
+  b->rank_mask_w = h_stats[6]; b->rank_mask_m = h_stats[7];
   b->n_services = d->n_units ? h_stats[3] + 1 : 0;
   b->sealed = true;
   *out = b;
@@ -703,7 +709,7 @@ constexpr uint64_t kMinOrderedUnits = 131072;  // the order costs ~10 us per lau
 static void result_release(fm_result *r) {
   if (!r->ctx) { delete r; return; }
   cudaStream_t st = r->ctx->stream;
-  void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts, r->d_order,
+  void *ptrs[] = {r->d_params, r->d_scores, r->d_unit_status, r->d_unit_points, r->d_counts, r->d_order, r->d_rank_classes,
                   r->d_worst, r->d_verdicts, r->d_band_up, r->d_band_lo, r->d_anom_off, r->d_anom_idx, r->d_anom_val};
   for (void *p : ptrs)
     if (p) cudaFreeAsync(p, st);
@@ -749,6 +755,8 @@ static int result_alloc(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
   FM_R(cudaMallocAsync(&r->d_unit_points, (n + 1) * sizeof(uint32_t), st));
   static const bool no_order = getenv("FOREMAST_GPU_NO_ORDER") != nullptr;  // A/B switch for scripts/ragged_time.py
   if (n >= kMinOrderedUnits && !no_order) FM_R(cudaMallocAsync(&r->d_order, (n + 1) * sizeof(uint32_t), st));
+  const bool mixed = ((b->rank_mask_w & (b->rank_mask_w - 1u)) | (b->rank_mask_m & (b->rank_mask_m - 1u))) != 0;
+  if (mixed && p->pairwise != FM_PW_NONE) FM_R(cudaMallocAsync(&r->d_rank_classes, (2 * n + 64) * sizeof(uint32_t), st));
   FM_R(cudaMallocAsync(&r->d_counts, (4 * ns + 4) * sizeof(uint32_t), st));
   FM_R(cudaMallocAsync(&r->d_worst, (ns + 1) * sizeof(unsigned long long), st));
   FM_R(cudaMallocAsync(&r->d_verdicts, (ns + 1) * sizeof(fm_verdict), st));
@@ -782,8 +790,10 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
   uint32_t *ustat = r->d_unit_status + i0, *upts = r->d_unit_points + i0;
   if (timed) FM_R(cudaEventRecord(r->ev[1], st));
   if (do_rank)
+    // (the class scratch is laid out for the whole batch: hist | list_w[n] | list_m[n]; a range uses its own part of it)
     FM_R(fm_launch_rank(db, r->d_params, p->pairwise, b->max_base, b->max_cur, scores, ctx->sm_count, st,
-                        timed ? r->ev[2] : nullptr));
+                        timed ? r->ev[2] : nullptr, b->rank_mask_w, b->rank_mask_m,
+                        r->d_rank_classes && i0 == 0 && i1 == b->n_units ? r->d_rank_classes : nullptr));
   else if (timed)
     FM_R(cudaEventRecord(r->ev[2], st));
   if (timed) FM_R(cudaEventRecord(r->ev[3], st));

@@ -54,6 +54,18 @@ struct DevParams {
   double hw_w[2 * 64];
 };
 
+// Sort-size class of a segment of n samples in the rank kernels: the sizes are 32 * {1,2,3,4,6,8,12,16,24,32,48,64} slots.
+// Segments that are not ranked at all (empty, or longer than 2048: D17) count as class 0.
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+static inline uint32_t fm_rank_class(uint32_t n) {
+  if (n > 2048u) return 0u;
+  return n <= 32 ? 0u : n <= 64 ? 1u : n <= 96 ? 2u : n <= 128 ? 3u : n <= 192 ? 4u : n <= 256 ? 5u : n <= 384 ? 6u
+         : n <= 512 ? 7u : n <= 768 ? 8u : n <= 1024 ? 9u : n <= 1536 ? 10u : 11u;
+}
+constexpr uint32_t kRankClassSize[12] = {32, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048};
+
 // Lanes the tensor-memory Holt-Winters kernel uses for one season: the largest divisor of the period that is at
 // most 32, provided it leaves at most 64 samples per lane and at least half the warp busy; 0 = use k_hw.
 static inline uint32_t fm_hw_tm_lanes(uint32_t period) {
@@ -92,8 +104,12 @@ __device__ __forceinline__ void cp_async_wait() {
 void fm_launch_synth(const fm_synth_config &cfg, uint64_t stride, float *values, int64_t *offsets,
                      uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type, cudaStream_t st);
 void fm_launch_batch_stats(const DevBatch &b, uint32_t *out6, cudaStream_t st);
+// mask_w / mask_m: the sort-size classes (fm_rank_class) present among the units' pair counts min(n_base, n_cur) and
+// longer segments max(n_base, n_cur), 0 = not known.  With more than one class and a scratch of 2 * n_units + 64 words
+// the units are grouped by class and every class runs in its own network; otherwise all run in the largest.
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
-                           fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon);
+                           fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon,
+                           uint32_t mask_w = 0, uint32_t mask_m = 0, uint32_t *class_scratch = nullptr);
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
                            float *band_up, float *band_lo, cudaStream_t st);

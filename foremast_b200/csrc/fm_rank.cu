@@ -254,18 +254,38 @@ __device__ __noinline__ double p_wilcoxon(long long wp2, long long wm2, uint32_t
 // pass: each keeps its instruction footprint inside the instruction cache (one fused kernel lost 4-5
 // issue slots per issued instruction to fetch stalls), and both are bound by instruction issue, so the
 // second read of the samples (from L2/HBM) costs nothing measurable.
-template <int R>
+// The units a launch covers: all of the batch (list == nullptr), or the units of ONE sort-size class of a batch that has
+// several -- list holds the unit indices grouped by class, hist[c] the class sizes (fm_rank_classes below), so a batch
+// of short windows with a few long ones among them does not sort every unit in the long ones' network.
+struct UnitSet {
+  const uint32_t *list;
+  const uint32_t *hist;
+  int cls;
+};
+template <bool LISTED>  // a template parameter of the kernels: the all-units form must not pay for the other (it did: + 8 %)
+__device__ __forceinline__ uint64_t unit_set_begin(const UnitSet &us, const DevBatch &b, const uint32_t *&lst) {
+  if (!LISTED) { lst = nullptr; return b.n_units; }
+  uint32_t off = 0;
+  for (int c = 0; c < us.cls; ++c) off += us.hist[c];
+  lst = us.list + off;
+  return us.hist[us.cls];
+}
+
+template <int R, bool LISTED>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxon(DevBatch b, const DevParams *__restrict__ dp,
                                                                                   fm_series_score *__restrict__ scores,
-                                                                                  const int raw_cap) {
+                                                                                  const int raw_cap, const UnitSet us) {
   extern __shared__ uint32_t s_tiles[];  // [warps][2][raw_cap] staged samples (the sorted keys never leave the registers)
   const unsigned lane = fm_lane(), warp = threadIdx.x >> 5;
   const uint32_t pairwise = dp->pairwise;
   const bool want_w = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY || pairwise == FM_PW_WILCOXON;
   float *const rawA = reinterpret_cast<float *>(s_tiles) + (size_t)warp * 2 * raw_cap;
   float *const rawB = rawA + raw_cap;
-  auto stage_pairs = [&](uint64_t uu) {
-    if (uu < b.n_units) {
+  const uint32_t *lst;
+  const uint64_t n_set = unit_set_begin<LISTED>(us, b, lst);  // positions 0 .. n_set-1 of this launch; unit = lst ? lst[pos] : pos
+  auto stage_pairs = [&](uint64_t pos) {
+    if (pos < n_set) {
+      const uint64_t uu = LISTED ? lst[pos] : pos;
       const int64_t o = b.offsets[uu];
       const uint32_t h0 = b.seg_lens[3 * uu], n1 = b.seg_lens[3 * uu + 1], n2 = b.seg_lens[3 * uu + 2];
       const uint32_t mm = min(min(n1, n2), (uint32_t)raw_cap);
@@ -280,10 +300,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxo
   stage_pairs((uint64_t)blockIdx.x * kWarpsPerBlock + warp);
 
   // Rounds: in round i warp w of block c owns unit (i*gridDim + c)*kWarpsPerBlock + w.
-  const uint64_t n_rounds = (b.n_units + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
+  const uint64_t n_rounds = (n_set + (uint64_t)gridDim.x * kWarpsPerBlock - 1) / ((uint64_t)gridDim.x * kWarpsPerBlock);
   for (uint64_t round = 0; round < n_rounds; ++round) {
-    const uint64_t u = (round * gridDim.x + blockIdx.x) * kWarpsPerBlock + warp;
-    const bool have = u < b.n_units;
+    const uint64_t pos = (round * gridDim.x + blockIdx.x) * kWarpsPerBlock + warp;
+    const bool have = pos < n_set;
+    const uint64_t u = LISTED && have ? lst[pos] : pos;
     uint32_t nb = 0, nc = 0;
     if (have) { nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2]; }
     const uint32_t m = min(nb, nc);  // the pairs are the first m samples of each segment (D8)
@@ -294,7 +315,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxo
     cp_async_wait<0>();
     __syncwarp();
     if (!run_w) {  // nothing to rank here, but the staging pipeline must keep moving
-      stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
+      stage_pairs(pos + (uint64_t)gridDim.x * kWarpsPerBlock);
     } else {
       uint32_t key[R];
       uint32_t nz = 0;
@@ -314,7 +335,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, R > 32 ? 1 : 3) k_wilcoxo
       }
       const uint32_t n_valid = w_n = __reduce_add_sync(0xffffffffu, nz);
       __syncwarp();  // every lane has its keys in registers: the staging buffers are free again
-      stage_pairs(u + (uint64_t)gridDim.x * kWarpsPerBlock);
+      stage_pairs(pos + (uint64_t)gridDim.x * kWarpsPerBlock);
       warp_bitonic_sort<R>(key, lane);
 
       // ties between neighbours of the sorted run (the lane holds elements lane*R .. lane*R+R-1); the keys
@@ -394,10 +415,10 @@ struct LowerBound {
 // Shared memory per warp: tile u32[N+4] | current keys u32[key_words] (raw floats first; the
 // representative's id for keys that turn out to have one) | id table u16[n_slots] of the rounds, whose
 // bytes afterwards hold the per-id counters u16[N] and the baseline's run lengths u16[rl_entries].
-template <int R, int W>
+template <int R, int W, bool LISTED>
 __global__ void __launch_bounds__(W * 32, R <= 24 ? 3 : 1) k_mw(DevBatch b, const DevParams *__restrict__ dp,
                                                                 fm_series_score *__restrict__ scores, const int rl_entries,
-                                                                const int key_words, const int n_slots) {
+                                                                const int key_words, const int n_slots, const UnitSet us) {
   constexpr int N = 32 * R;
   constexpr int kTileWords = N + 4;
   constexpr int CH = R % 8 == 0 ? 8 : (R <= 6 ? R : 4);  // keys per chunk of the rolled loops
@@ -443,12 +464,16 @@ __global__ void __launch_bounds__(W * 32, R <= 24 ? 3 : 1) k_mw(DevBatch b, cons
   };
 
   const uint64_t stride_units = (uint64_t)gridDim.x * W;
-  for (uint64_t u = (uint64_t)blockIdx.x * W + warp; u < b.n_units; u += stride_units) {
+  const uint32_t *lst;
+  const uint64_t n_set = unit_set_begin<LISTED>(us, b, lst);
+  for (uint64_t pos = (uint64_t)blockIdx.x * W + warp; pos < n_set; pos += stride_units) {
+    const uint64_t u = LISTED ? lst[pos] : pos;
     const int64_t off = b.offsets[u];
     const uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
     {  // pull the next round's samples towards L2 while this round works
-      const uint64_t un = u + stride_units;
-      if (un < b.n_units) {
+      const uint64_t pn = pos + stride_units;
+      if (pn < n_set) {
+        const uint64_t un = LISTED ? lst[pn] : pn;
         const int64_t offn = b.offsets[un];
         const uint32_t nhn = b.seg_lens[3 * un], len = b.seg_lens[3 * un + 1] + b.seg_lens[3 * un + 2];
         const char *p = reinterpret_cast<const char *>(b.values + offn + nhn);
@@ -683,22 +708,63 @@ __global__ void __launch_bounds__(256) k_rank_finalize(DevBatch b, const DevPara
 constexpr uint64_t kBlocksPerSm = 64;  // many more blocks than are resident: tie-heavy units take longer, the block
                                        // scheduler evens it out (a persistent 5-blocks-per-SM grid measured 19 % slower)
 
+// ---- grouping the units of a mixed batch by sort-size class -----------------------------------------
+// hist[0..11]: class sizes by pair count (Wilcoxon), hist[12..23]: by longer segment (Mann-Whitney / Kruskal);
+// cursor = hist + 24.  One atomic per class and warp (match.any), not per unit.
+__device__ __forceinline__ uint32_t warp_class_slot(uint32_t cls, uint32_t *counter, unsigned lane) {
+  const unsigned peers = __match_any_sync(0xffffffffu, cls);
+  const int leader = __ffs(peers) - 1;
+  uint32_t base = 0;
+  if ((int)lane == leader) base = atomicAdd(counter + cls, (uint32_t)__popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  return base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+__global__ void __launch_bounds__(256) k_rank_class_hist(DevBatch b, uint32_t *__restrict__ hist) {
+  const uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t nb = 0, nc = 0;
+  if (u < b.n_units) { nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2]; }
+  // lanes past the end count into class 0 of a third, unused histogram
+  const unsigned lane = fm_lane();
+  warp_class_slot(u < b.n_units ? fm_rank_class(min(nb, nc)) : 36u, hist, lane);
+  warp_class_slot(u < b.n_units ? 12u + fm_rank_class(max(nb, nc)) : 37u, hist, lane);
+}
+__global__ void __launch_bounds__(256) k_rank_class_scatter(DevBatch b, uint32_t *__restrict__ hist, uint32_t *__restrict__ list_w,
+                                                            uint32_t *__restrict__ list_m) {
+  const uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool have = u < b.n_units;
+  uint32_t nb = 0, nc = 0;
+  if (have) { nb = b.seg_lens[3 * u + 1]; nc = b.seg_lens[3 * u + 2]; }
+  const unsigned lane = fm_lane();
+  uint32_t *const cursor = hist + 40;
+  const uint32_t cw = have ? fm_rank_class(min(nb, nc)) : 36u, cm = have ? 12u + fm_rank_class(max(nb, nc)) : 37u;
+  const uint32_t pw = warp_class_slot(cw, cursor, lane), pm = warp_class_slot(cm, cursor, lane);
+  if (have) {
+    uint32_t ow = 0, om = 0;
+    for (uint32_t c = 0; c < cw; ++c) ow += hist[c];
+    for (uint32_t c = 12; c < cm; ++c) om += hist[c];
+    list_w[ow + pw] = (uint32_t)u;
+    list_m[om + pm] = (uint32_t)u;
+  }
+}
+
 template <int R>
 cudaError_t launch_wilcoxon(const DevBatch &b, const DevParams *dp, uint32_t max_pairs, fm_series_score *scores, int sm_count,
-                            cudaStream_t st) {
+                            cudaStream_t st, UnitSet us = UnitSet{nullptr, nullptr, 0}) {
   const uint64_t blocks = std::min<uint64_t>((b.n_units + kWarpsPerBlock - 1) / kWarpsPerBlock, (uint64_t)sm_count * kBlocksPerSm);
   if (blocks == 0) return cudaSuccess;
   const int raw_cap = ((int)std::min<uint32_t>(max_pairs, 32u * R) + 3) & ~3;
   const int smem = kWarpsPerBlock * 2 * raw_cap * 4;
-  cudaError_t e = cudaFuncSetAttribute(k_wilcoxon<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaError_t e = us.list ? cudaFuncSetAttribute(k_wilcoxon<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                          : cudaFuncSetAttribute(k_wilcoxon<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  k_wilcoxon<R><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, raw_cap);
+  if (us.list) k_wilcoxon<R, true><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, raw_cap, us);
+  else k_wilcoxon<R, false><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, st>>>(b, dp, scores, raw_cap, us);
   return cudaGetLastError();
 }
 
 template <int R>
 cudaError_t launch_mw(const DevBatch &b, const DevParams *dp, uint32_t max_seg, fm_series_score *scores, int sm_count,
-                      cudaStream_t st) {
+                      cudaStream_t st, UnitSet us = UnitSet{nullptr, nullptr, 0}) {
   constexpr int W = R >= 48 ? 4 : (R == 32 ? 6 : 8);
   constexpr int N = 32 * R;
   const int seg_cap = (int)std::min<uint32_t>(max_seg, 32u * R);
@@ -710,11 +776,13 @@ cudaError_t launch_mw(const DevBatch &b, const DevParams *dp, uint32_t max_seg, 
   int n_slots = std::max(std::max(N + rl_cap, seg_cap + seg_cap / 4), std::min(budget / 2, 4 * seg_cap));
   n_slots = (n_slots + 7) & ~7;
   const int smem = W * ((N + 4) + key_words + n_slots / 2) * 4;
-  cudaError_t e = cudaFuncSetAttribute(k_mw<R, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaError_t e = us.list ? cudaFuncSetAttribute(k_mw<R, W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                          : cudaFuncSetAttribute(k_mw<R, W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   const uint64_t blocks = std::min<uint64_t>((b.n_units + W - 1) / W, (uint64_t)sm_count * kBlocksPerSm);
   if (blocks == 0) return cudaSuccess;
-  k_mw<R, W><<<(unsigned)blocks, W * 32, smem, st>>>(b, dp, scores, rl_cap, key_words, n_slots);
+  if (us.list) k_mw<R, W, true><<<(unsigned)blocks, W * 32, smem, st>>>(b, dp, scores, rl_cap, key_words, n_slots, us);
+  else k_mw<R, W, false><<<(unsigned)blocks, W * 32, smem, st>>>(b, dp, scores, rl_cap, key_words, n_slots, us);
   return cudaGetLastError();
 }
 
@@ -730,7 +798,8 @@ cudaError_t launch_mw(const DevBatch &b, const DevParams *dp, uint32_t max_seg, 
 // FM_RANK_MAX_SEGMENT samples are not ranked (D17: Mann-Whitney / Kruskal need both segments within the
 // limit, Wilcoxon its min(n_base, n_cur) pairs); the sort size is chosen for the rest.
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
-                           fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon) {
+                           fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon,
+                           uint32_t mask_w, uint32_t mask_m, uint32_t *class_scratch) {
   const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
   const bool w = all || pairwise == FM_PW_WILCOXON;
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
@@ -738,12 +807,41 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
   const uint32_t max_pairs = std::min(std::min(max_base, max_cur), cap);  // bounds min(n_base, n_cur) of every unit
   const uint32_t max_seg = std::min(std::max(max_base, max_cur), cap);
   cudaError_t e = cudaSuccess;
-#define FM_W(R) launch_wilcoxon<R>(b, dp, max_pairs, scores, sm_count, st)
-#define FM_M(R) launch_mw<R>(b, dp, max_seg, scores, sm_count, st)
-  if (w) e = FM_FOR_SORT_SIZE(max_pairs, FM_W);
+  // several sort sizes in the batch: group the units by class, one launch per class that occurs
+  const bool split_w = w && class_scratch && (mask_w & (mask_w - 1u)) != 0;
+  const bool split_m = pooled && class_scratch && (mask_m & (mask_m - 1u)) != 0;
+  uint32_t *const hist = class_scratch, *const list_w = class_scratch + 64, *const list_m = list_w + b.n_units;
+  if ((split_w || split_m) && b.n_units) {
+    e = cudaMemsetAsync(hist, 0, 64 * sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
+    const unsigned blocks = (unsigned)((b.n_units + 255) / 256);
+    k_rank_class_hist<<<blocks, 256, 0, st>>>(b, hist);
+    k_rank_class_scatter<<<blocks, 256, 0, st>>>(b, hist, list_w, list_m);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+#define FM_W(R) launch_wilcoxon<R>(b, dp, pairs_c, scores, sm_count, st, us)
+#define FM_M(R) launch_mw<R>(b, dp, seg_c, scores, sm_count, st, us)
+  if (w) {
+    for (int c = 0; c < 12 && e == cudaSuccess; ++c) {
+      if (split_w && !((mask_w >> c) & 1u)) continue;
+      if (!split_w && c) break;
+      const uint32_t pairs_c = split_w ? std::min(kRankClassSize[c], max_pairs) : max_pairs;
+      const UnitSet us = split_w ? UnitSet{list_w, hist, c} : UnitSet{nullptr, nullptr, 0};
+      e = FM_FOR_SORT_SIZE(pairs_c, FM_W);
+    }
+  }
   if (e != cudaSuccess) return e;
   if (after_wilcoxon) cudaEventRecord(after_wilcoxon, st);
-  if (pooled) e = FM_FOR_SORT_SIZE(max_seg, FM_M);
+  if (pooled) {
+    for (int c = 0; c < 12 && e == cudaSuccess; ++c) {
+      if (split_m && !((mask_m >> c) & 1u)) continue;
+      if (!split_m && c) break;
+      const uint32_t seg_c = split_m ? std::min(kRankClassSize[c], max_seg) : max_seg;
+      const UnitSet us = split_m ? UnitSet{list_m, hist + 12, c} : UnitSet{nullptr, nullptr, 0};
+      e = FM_FOR_SORT_SIZE(seg_c, FM_M);
+    }
+  }
   if (e != cudaSuccess) return e;
 #undef FM_W
 #undef FM_M

@@ -127,12 +127,14 @@ __global__ void __launch_bounds__(256) k_synth(fm_synth_config cfg, uint64_t str
   }
 }
 
-// out6 = {max n_hist, max n_base, max n_cur, max service_id, #misaligned offsets, #overlapping units}
+// out6 = {max n_hist, max n_base, max n_cur, max service_id, #misaligned offsets, #overlapping units,
+//         rank sort-size classes present by pair count, by longer segment (fm_rank_class)}
 __global__ void __launch_bounds__(256) k_batch_stats(DevBatch b, uint32_t *out6) {
-  uint32_t mh = 0, mb = 0, mc = 0, ms = 0, bad = 0, ovl = 0;
+  uint32_t mh = 0, mb = 0, mc = 0, ms = 0, bad = 0, ovl = 0, kw = 0, km = 0;
   for (uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u < b.n_units; u += (uint64_t)gridDim.x * blockDim.x) {
     uint32_t nh = b.seg_lens[3 * u], nb = b.seg_lens[3 * u + 1], nc = b.seg_lens[3 * u + 2];
     mh = max(mh, nh); mb = max(mb, nb); mc = max(mc, nc);
+    kw |= 1u << fm_rank_class(min(nb, nc)); km |= 1u << fm_rank_class(max(nb, nc));
     ms = max(ms, b.service_id[u]);
     int64_t o = b.offsets[u], o1 = b.offsets[u + 1];
     bad += (o & 3) != 0 || o < 0;
@@ -141,10 +143,12 @@ __global__ void __launch_bounds__(256) k_batch_stats(DevBatch b, uint32_t *out6)
   mh = __reduce_max_sync(0xffffffffu, mh); mb = __reduce_max_sync(0xffffffffu, mb);
   mc = __reduce_max_sync(0xffffffffu, mc); ms = __reduce_max_sync(0xffffffffu, ms);
   bad = __reduce_add_sync(0xffffffffu, bad); ovl = __reduce_add_sync(0xffffffffu, ovl);
+  kw = __reduce_or_sync(0xffffffffu, kw); km = __reduce_or_sync(0xffffffffu, km);
   if ((threadIdx.x & 31) == 0) {
     atomicMax(out6 + 0, mh); atomicMax(out6 + 1, mb); atomicMax(out6 + 2, mc); atomicMax(out6 + 3, ms);
     if (bad) atomicAdd(out6 + 4, bad);
     if (ovl) atomicAdd(out6 + 5, ovl);
+    atomicOr(out6 + 6, kw); atomicOr(out6 + 7, km);
   }
 }
 

@@ -283,6 +283,31 @@ def test_ragged_large_batch_takes_the_ordered_band_path(ctx, oracle):
     b.free()
 
 
+def test_mixed_sort_sizes_run_per_class(ctx, oracle):
+    """A batch whose units need different sort sizes in the rank kernels (short canary windows with long ones and
+    over-long ones among them) is grouped by size class and every class runs in its own network; before, one long unit
+    put all of them into the largest.  Scores against the oracle for every pairwise mode."""
+    rng = np.random.default_rng(21)
+    n = 3000
+    lens = rng.choice([1, 7, 30, 33, 64, 65, 100, 190, 257, 500, 760, 1000, 1500, 2048, 2100, 2600], (n, 2))
+    units = []
+    for nb, nc in lens:
+        kind = rng.integers(0, 3)
+        z = rng.normal(10, 2, nb + nc) if kind == 0 else np.round(rng.normal(10, 2, nb + nc)) if kind == 1 else np.full(nb + nc, 3.0)
+        units.append(([], z[:nb].astype(np.float32), z[nb:].astype(np.float32)))
+    sid = np.arange(n) // 10
+    mts = rng.integers(0, 8, n)
+    p = full_params(oracle, abi.ALG_MA_ALL, abi.PW_ALL)
+    b = ctx.batch_from_units(units, service_id=sid, metric_type=mts)
+    got, _ = check_batch(ctx, oracle, b, p)
+    ran = got["status"] & (abi.S_MW_RUN | abi.S_WILCOXON_RUN | abi.S_KRUSKAL_RUN)
+    assert (ran != 0).mean() > 0.5 and (ran == 0).any()   # the over-long ones are not ranked (D17)
+    for pw in (abi.PW_WILCOXON, abi.PW_MANN_WHITE, abi.PW_KRUSKAL):
+        p.pairwise = pw
+        check_batch(ctx, oracle, b, p)
+    b.free()
+
+
 @pytest.mark.parametrize("period,hist", [(96, 500), (1440, 4400), (100, 777)])
 def test_model_cache_continuous_mode(ctx, oracle, period, hist):
     """Continuous mode: fit Holt-Winters once, then score successive current windows from the cached
