@@ -232,9 +232,16 @@ __device__ __forceinline__ void cur_fast(State<ALGS> &s, const FastRule &fr, dou
     const bool need = valid & (!roll_clear(a1, a2, c, d, xd, s.x0, fr) | (j == lag.last_j));
     bool f = fr.lo_on & (xd < fr.mlb);  // the clamp of the lower band is a plain comparison
     if (need) {
-      const RollExact e = roll_exact(a1, a2, cnt, s.x0, fr.k, fr.mlb, (fr.up_on ? 1u : 0u) | (fr.lo_on ? 2u : 0u), xd);
-      f = e.flag;
-      s.rsd = e.sd;
+      // A flat window with the point on it (a gauge that does not move, an error count that stays 0: common) is the
+      // one case the filter can never clear, since V = 0.  The oracle's arithmetic on it is exact: a1 = a2 = 0 and
+      // x = x0 give mean = x0, sd = 0, up = lo = x0, so only the lower clamp (f already holds it) can flag the point.
+      if ((a1 == 0.0) & (a2 == 0.0) & (d == 0.0)) {
+        s.rsd = 0.0;
+      } else {
+        const RollExact e = roll_exact(a1, a2, cnt, s.x0, fr.k, fr.mlb, (fr.up_on ? 1u : 0u) | (fr.lo_on ? 2u : 0u), xd);
+        f = e.flag;
+        s.rsd = e.sd;
+      }
     }
     if (f) mask[3] |= 1u << i;
     if (DEEP) roll_advance_deep<ALGS, K>(s, xd, *dl, i);
