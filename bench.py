@@ -531,9 +531,10 @@ def run_ours(args):
                     # and the host memory system allow; the call's own time as a fraction of it
                     "bare_h2d_copy_ms": copy_ms or None,
                     "frac_of_bare_copy": (copy_ms / e2e_ms) if copy_ms else None},
-            # inside the timed region, per step: k_wilcoxon, k_mw, k_rank_finalize, k_band, k_verdict_reduce,
-            # k_verdict_finalize (+ NCCL's own all-reduce kernel at N > 1, not counted: it is not ours)
-            "gpu_launches": 6 * args.steps,
+            # inside the timed region, per step: k_wilcoxon, k_mw, k_rank_finalize, k_band_order (launches of 131 072
+            # units and more), k_band, k_verdict_reduce, k_verdict_finalize (+ NCCL's own all-reduce kernel at N > 1,
+            # not counted: it is not ours)
+            "gpu_launches": (7 if n >= 131072 and not os.environ.get("FOREMAST_GPU_NO_ORDER") else 6) * args.steps,
             # the untimed legs: the parity pass, the per-scorer passes, the e2e calls (the five scoring kernels once per
             # ~256 MiB upload chunk + one finalize), cfg2 / cfg4 / cfg0 / ingest, their generators
             "gpu_launches_other_legs": 6 + 5 * 8 * 2 + (e2e_steps + 1) * (5 * (-(-pv.nbytes // (256 << 20))) + 1) + 1
