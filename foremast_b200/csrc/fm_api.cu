@@ -790,10 +790,10 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
   uint32_t *ustat = r->d_unit_status + i0, *upts = r->d_unit_points + i0;
   if (timed) FM_R(cudaEventRecord(r->ev[1], st));
   if (do_rank)
-    // (the class scratch is laid out for the whole batch: hist | list_w[n] | list_m[n]; a range uses its own part of it)
+    // (class scratch: 64 words of class sizes and cursors, then 2 n unit indices; a range uses the 2 (i1 - i0) at 2 i0)
     FM_R(fm_launch_rank(db, r->d_params, p->pairwise, b->max_base, b->max_cur, scores, ctx->sm_count, st,
-                        timed ? r->ev[2] : nullptr, b->rank_mask_w, b->rank_mask_m,
-                        r->d_rank_classes && i0 == 0 && i1 == b->n_units ? r->d_rank_classes : nullptr));
+                        timed ? r->ev[2] : nullptr, b->rank_mask_w, b->rank_mask_m, r->d_rank_classes,
+                        r->d_rank_classes ? r->d_rank_classes + 64 + 2 * i0 : nullptr));
   else if (timed)
     FM_R(cudaEventRecord(r->ev[2], st));
   if (timed) FM_R(cudaEventRecord(r->ev[3], st));

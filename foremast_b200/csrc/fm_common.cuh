@@ -105,11 +105,13 @@ void fm_launch_synth(const fm_synth_config &cfg, uint64_t stride, float *values,
                      uint32_t *seg_lens, uint32_t *service_id, uint8_t *metric_type, cudaStream_t st);
 void fm_launch_batch_stats(const DevBatch &b, uint32_t *out6, cudaStream_t st);
 // mask_w / mask_m: the sort-size classes (fm_rank_class) present among the units' pair counts min(n_base, n_cur) and
-// longer segments max(n_base, n_cur), 0 = not known.  With more than one class and a scratch of 2 * n_units + 64 words
-// the units are grouped by class and every class runs in its own network; otherwise all run in the largest.
+// longer segments max(n_base, n_cur), 0 = not known.  With more than one class, a scratch of 64 words and room for
+// 2 * n_units unit indices, the units are grouped by class and every class runs in its own network; otherwise all
+// run in the largest.
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
                            fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon,
-                           uint32_t mask_w = 0, uint32_t mask_m = 0, uint32_t *class_scratch = nullptr);
+                           uint32_t mask_w = 0, uint32_t mask_m = 0, uint32_t *class_scratch = nullptr,
+                           uint32_t *class_lists = nullptr);
 cudaError_t fm_launch_band(const DevBatch &b, const DevParams *dp, uint32_t algorithms, bool rank_ran,
                            fm_series_score *scores, uint32_t *unit_status, uint32_t *unit_points,
                            float *band_up, float *band_lo, cudaStream_t st);

@@ -799,7 +799,7 @@ cudaError_t launch_mw(const DevBatch &b, const DevParams *dp, uint32_t max_seg, 
 // limit, Wilcoxon its min(n_base, n_cur) pairs); the sort size is chosen for the rest.
 cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pairwise, uint32_t max_base, uint32_t max_cur,
                            fm_series_score *scores, int sm_count, cudaStream_t st, cudaEvent_t after_wilcoxon,
-                           uint32_t mask_w, uint32_t mask_m, uint32_t *class_scratch) {
+                           uint32_t mask_w, uint32_t mask_m, uint32_t *class_scratch, uint32_t *class_lists) {
   const bool all = pairwise == FM_PW_ALL || pairwise == FM_PW_ANY;
   const bool w = all || pairwise == FM_PW_WILCOXON;
   const bool pooled = all || pairwise == FM_PW_MANN_WHITE || pairwise == FM_PW_KRUSKAL;
@@ -808,9 +808,9 @@ cudaError_t fm_launch_rank(const DevBatch &b, const DevParams *dp, uint32_t pair
   const uint32_t max_seg = std::min(std::max(max_base, max_cur), cap);
   cudaError_t e = cudaSuccess;
   // several sort sizes in the batch: group the units by class, one launch per class that occurs
-  const bool split_w = w && class_scratch && (mask_w & (mask_w - 1u)) != 0;
-  const bool split_m = pooled && class_scratch && (mask_m & (mask_m - 1u)) != 0;
-  uint32_t *const hist = class_scratch, *const list_w = class_scratch + 64, *const list_m = list_w + b.n_units;
+  const bool split_w = w && class_scratch && class_lists && (mask_w & (mask_w - 1u)) != 0;
+  const bool split_m = pooled && class_scratch && class_lists && (mask_m & (mask_m - 1u)) != 0;
+  uint32_t *const hist = class_scratch, *const list_w = class_lists, *const list_m = class_lists + b.n_units;
   if ((split_w || split_m) && b.n_units) {
     e = cudaMemsetAsync(hist, 0, 64 * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;

@@ -465,6 +465,21 @@ def test_score_host_pipelined_chunks(ctx, oracle, monkeypatch):
             monkeypatch.delenv("FOREMAST_GPU_CHUNK_BYTES", raising=False)
         assert ctx.score_host(h, p).tobytes() == want
         assert ctx.score_host(h, p, h.n_services + 5)[:h.n_services].tobytes() == want
+    # units of several rank sort sizes: every upload chunk groups its own units by size class
+    rng = np.random.default_rng(4)
+    units = []
+    for nb, nc in rng.choice([5, 30, 40, 70, 130, 300, 700], (1500, 2)):
+        z = np.round(rng.normal(20, 3, nb + nc), int(rng.integers(0, 3))).astype(np.float32)
+        units.append(([], z[:nb], z[nb:]))
+    hm = abi.HostCsr.from_units(units, np.arange(1500) // 6, rng.integers(0, 8, 1500))
+    ref, _, _ = oracle.score(hm, p)
+    want = oracle.verdicts(hm, ref, hm.n_services).tobytes()
+    for chunk in ("65536", None):
+        if chunk:
+            monkeypatch.setenv("FOREMAST_GPU_CHUNK_BYTES", chunk)
+        else:
+            monkeypatch.delenv("FOREMAST_GPU_CHUNK_BYTES", raising=False)
+        assert ctx.score_host(hm, p).tobytes() == want
 
 
 def test_bands_materialised(ctx, oracle):
