@@ -115,7 +115,10 @@ template <int R>
 __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsigned lane) {
   static_assert(odd_part(R) == 1 || odd_part(R) == 3, "R must be 2^q or 3*2^q");
   lane_sort<R>(v);
-#pragma unroll 1
+  // rolled for the long networks (instruction cache); the short ones (up to 128 slots) are small enough to be laid
+  // out flat, which saves the loop control and the run-time lane masks of their fifteen cross-lane steps
+  constexpr int kFlat = R <= 4 ? 5 : 1;
+#pragma unroll kFlat
   for (unsigned kk = 1; kk <= 16; kk <<= 1) {  // merges 2*kk lanes, L = R*kk elements a side
     {
       const unsigned lm = 2 * kk - 1;
@@ -132,7 +135,7 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsign
         v[R / 2] = sel_minmax(lower, v[R / 2], a);
       }
     }
-#pragma unroll 1
+#pragma unroll kFlat
     for (unsigned jj = kk >> 1; jj >= 1; jj >>= 1) {
       const bool lower = (lane & jj) == 0;
 #pragma unroll
