@@ -115,9 +115,9 @@ template <int R>
 __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&v)[R], const unsigned lane) {
   static_assert(odd_part(R) == 1 || odd_part(R) == 3, "R must be 2^q or 3*2^q");
   lane_sort<R>(v);
-  // rolled for the long networks (instruction cache); the short ones (up to 128 slots) are small enough to be laid
+  // rolled for the long networks (instruction cache); the short ones (up to 256 slots) are small enough to be laid
   // out flat, which saves the loop control and the run-time lane masks of their fifteen cross-lane steps
-  constexpr int kFlat = R <= 4 ? 5 : 1;
+  constexpr int kFlat = R <= 8 ? 5 : 1;
 #pragma unroll kFlat
   for (unsigned kk = 1; kk <= 16; kk <<= 1) {  // merges 2*kk lanes, L = R*kk elements a side
     {
