@@ -32,19 +32,21 @@ struct fm_ctx {
   unsigned char *arena_dev = nullptr, *arena_host = nullptr;
   DevParams arena_params;       // what the slab's DevParams currently holds
   bool arena_params_valid = false;
+  bool arena_clean = false;     // the result part of the slab is zero (cleared behind the previous call's download)
+  cudaEvent_t arena_done = nullptr;  // the previous call's verdicts have reached the host slab
 };
 
 namespace {
 constexpr uint64_t kArenaUnits = 1024, kArenaValues = 256 * 1024, kArenaServices = 1024;
 constexpr uint64_t a16(uint64_t x) { return (x + 255) & ~255ull; }
-// device slab layout (byte offsets); the host slab mirrors [values .. mt] for the single upload, then the verdicts
+// device slab layout (byte offsets); the host slab mirrors [params .. values] for the single upload, then the verdicts
 constexpr uint64_t kOffParams = 0;
-constexpr uint64_t kOffValues = a16(sizeof(DevParams));
-constexpr uint64_t kOffOffsets = kOffValues + a16((kArenaValues + 32) * 4);
-constexpr uint64_t kOffSeg = kOffOffsets + a16((kArenaUnits + 1) * 8);
+constexpr uint64_t kOffOffsets = a16(sizeof(DevParams));   // params | per-unit arrays | values: ONE upload, which ends
+constexpr uint64_t kOffSeg = kOffOffsets + a16((kArenaUnits + 1) * 8);   // where the job's samples end
 constexpr uint64_t kOffSid = kOffSeg + a16(3 * kArenaUnits * 4);
 constexpr uint64_t kOffMt = kOffSid + a16(kArenaUnits * 4);
-constexpr uint64_t kOffScores = kOffMt + a16(kArenaUnits);  // scores | counts | worst are cleared together
+constexpr uint64_t kOffValues = kOffMt + a16(kArenaUnits);
+constexpr uint64_t kOffScores = kOffValues + a16((kArenaValues + 32) * 4);  // scores | counts | worst are cleared together
 constexpr uint64_t kOffCounts = kOffScores + a16((kArenaUnits + 1) * sizeof(fm_series_score));
 constexpr uint64_t kOffWorst = kOffCounts + a16((4 * kArenaServices + 4) * 4);
 constexpr uint64_t kOffUstat = kOffWorst + a16((kArenaServices + 1) * 8);
@@ -399,6 +401,7 @@ void fm_shutdown(fm_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   if (ctx->arena_dev) cudaFree(ctx->arena_dev);
   if (ctx->arena_host) cudaFreeHost(ctx->arena_host);
+  if (ctx->arena_done) cudaEventDestroy(ctx->arena_done);
   for (auto &e : ctx->timer)
     if (e) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
@@ -776,7 +779,7 @@ static int result_alloc(fm_ctx *ctx, const fm_batch *b, const fm_params *p, fm_r
 
 // launch the scoring kernels over units [i0, i1) of the batch (results land at the same indices)
 static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_params *p, uint64_t i0, uint64_t i1,
-                        bool timed) {
+                        bool timed, bool small = false) {
   cudaStream_t st = ctx->stream;
   const bool do_rank = p->pairwise != FM_PW_NONE && b->max_base > 0 && b->max_cur > 0;
   DevBatch db = dev_view(b);
@@ -809,7 +812,8 @@ static int launch_range(fm_ctx *ctx, fm_result *r, const fm_batch *b, const fm_p
                       p->band_algorithm == FM_ALG_HW ? r->d_band_up : nullptr,
                       p->band_algorithm == FM_ALG_HW ? r->d_band_lo : nullptr, ctx->sm_count, st));
   if (timed) FM_R(cudaEventRecord(r->ev[4], st));
-  fm_launch_verdict_reduce(db, ustat, upts, r->n_services, r->d_counts, r->d_worst, st);
+  if (small) fm_launch_verdict_small(db, ustat, upts, r->n_services, r->d_counts, r->d_worst, r->d_verdicts, st);
+  else fm_launch_verdict_reduce(db, ustat, upts, r->n_services, r->d_counts, r->d_worst, st);
   FM_R(cudaGetLastError());
   if (timed) FM_R(cudaEventRecord(r->ev[5], st));
   return FM_OK;
@@ -1149,11 +1153,12 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
     if (!ctx->arena_dev) {
       FM_CUDA(ctx, cudaMalloc(&ctx->arena_dev, kArenaBytes));
       FM_CUDA(ctx, cudaMallocHost(&ctx->arena_host, kArenaBytes));
+      FM_CUDA(ctx, cudaEventCreateWithFlags(&ctx->arena_done, cudaEventDisableTiming));
     }
     unsigned char *dv = ctx->arena_dev, *hs = ctx->arena_host;
     DevParams hp;
     resolve_params(p, &hp);
-    uint64_t up0 = kOffValues;
+    uint64_t up0 = kOffOffsets;
     if (!ctx->arena_params_valid || memcmp(&hp, &ctx->arena_params, sizeof(hp)) != 0) {
       memcpy(hs + kOffParams, &hp, sizeof(hp));  // new parameters ride along with the samples
       ctx->arena_params = hp;
@@ -1166,16 +1171,12 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
     memcpy(hs + kOffSeg, h->seg_lens, 3 * n * 4);
     if (h->service_id) memcpy(hs + kOffSid, h->service_id, n * 4); else memset(hs + kOffSid, 0, n * 4);
     if (h->metric_type) memcpy(hs + kOffMt, h->metric_type, n); else memset(hs + kOffMt, 0, n);
-    // one upload: everything between the first byte that changed and the end of the per-unit arrays (the slab
-    // is laid out in upload order; the unused tail of the value area travels too when the batch is tiny, so
-    // the value area is copied separately once it is mostly empty)
-    if (n_vals * 4 + 128 < (kArenaValues * 4) / 8) {
-      FM_CUDA(ctx, cudaMemcpyAsync(dv + up0, hs + up0, kOffValues - up0 + (n_vals + 32) * 4, cudaMemcpyHostToDevice, st));
-      FM_CUDA(ctx, cudaMemcpyAsync(dv + kOffOffsets, hs + kOffOffsets, kOffScores - kOffOffsets, cudaMemcpyHostToDevice, st));
-    } else {
-      FM_CUDA(ctx, cudaMemcpyAsync(dv + up0, hs + up0, kOffScores - up0, cudaMemcpyHostToDevice, st));
-    }
-    FM_CUDA(ctx, cudaMemsetAsync(dv + kOffScores, 0, kOffUstat - kOffScores, st));
+    // one upload: from the first byte that changed (the parameters, or the per-unit arrays behind them) to the end
+    // of the job's samples -- the per-unit arrays travel whole (25 KB), which is cheaper than a second copy call
+    FM_CUDA(ctx, cudaMemcpyAsync(dv + up0, hs + up0, kOffValues + (n_vals + 32) * 4 - up0, cudaMemcpyHostToDevice, st));
+    // the result part of the slab is cleared BEHIND a call's download, off the next call's critical path
+    if (!ctx->arena_clean) FM_CUDA(ctx, cudaMemsetAsync(dv + kOffScores, 0, kOffUstat - kOffScores, st));
+    ctx->arena_clean = false;
     tb.d_values = reinterpret_cast<float *>(dv + kOffValues);
     tb.d_offsets = reinterpret_cast<int64_t *>(dv + kOffOffsets);
     tb.d_seg = reinterpret_cast<uint32_t *>(dv + kOffSeg);
@@ -1197,14 +1198,14 @@ int fm_score_host(fm_ctx *ctx, const fm_csr *h, const fm_params *p, uint32_t n_s
     sr.d_unit_status = reinterpret_cast<uint32_t *>(dv + kOffUstat);
     sr.d_unit_points = reinterpret_cast<uint32_t *>(dv + kOffUpts);
     sr.d_verdicts = reinterpret_cast<fm_verdict *>(dv + kOffVerdicts);
-    rc = launch_range(ctx, &sr, &tb, p, 0, n, false);
+    rc = launch_range(ctx, &sr, &tb, p, 0, n, false, /*small=*/true);  // its verdict kernel folds and finalises in one launch
     if (rc) { cudaStreamSynchronize(st); return rc; }
-    if (n_services) {
-      fm_launch_verdict_finalize(n_services, sr.d_counts, sr.d_worst, sr.d_verdicts, 0u, st);
-      FM_CUDA(ctx, cudaGetLastError());
+    if (n_services)
       FM_CUDA(ctx, cudaMemcpyAsync(hs + kOffVerdicts, sr.d_verdicts, n_services * sizeof(fm_verdict), cudaMemcpyDeviceToHost, st));
-    }
-    FM_CUDA(ctx, cudaStreamSynchronize(st));
+    FM_CUDA(ctx, cudaEventRecord(ctx->arena_done, st));
+    const cudaError_t ce = cudaMemsetAsync(dv + kOffScores, 0, kOffUstat - kOffScores, st);  // for the next call
+    FM_CUDA(ctx, cudaEventSynchronize(ctx->arena_done));
+    ctx->arena_clean = ce == cudaSuccess;
     if (n_services) memcpy(verdicts, hs + kOffVerdicts, n_services * sizeof(fm_verdict));
     return FM_OK;
   }

@@ -142,3 +142,5 @@ void fm_launch_verdict_reduce(const DevBatch &b, const uint32_t *unit_status, co
                               uint32_t n_services, uint32_t *counts, unsigned long long *worst, cudaStream_t st);
 void fm_launch_verdict_finalize(uint32_t n_services, const uint32_t *counts, const unsigned long long *worst,
                                 fm_verdict *out, uint32_t first_service, cudaStream_t st);
+void fm_launch_verdict_small(const DevBatch &b, const uint32_t *unit_status, const uint32_t *unit_points,
+                             uint32_t n_services, uint32_t *counts, unsigned long long *worst, fm_verdict *out, cudaStream_t st);
