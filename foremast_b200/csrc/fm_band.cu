@@ -136,6 +136,21 @@ __device__ __forceinline__ void src_update(State<ALGS> &s, double xd, double alp
   }
 }
 
+// ---- forecast bands (EWMA, DES) without the band arithmetic per point -----------------------------------
+// The oracle flags x against up = fma(k, sig, f) and lo = fma(-k, sig, f).  With e = fl(x - f) and K = k sig,
+// x > up needs x - f > K - u (K + |f|) (u = 2^-53, the rounding of up), and symmetrically below.  So
+//     |e| <= fl(K) (1 - 2^-30) - 2^-40 (|f| + |x|)
+// proves the point inside: the two margins exceed the roundings of e, of fl(K), of up / lo and of this test itself
+// (each at most a few u of K + |f| + |x|) by factors of 2^20 and 2^10.  Points that fail it -- anomalies, points
+// within 1e-9 of an edge, NaNs (every comparison false) -- take the oracle's arithmetic, so flags stay bit-identical;
+// x < min_lower_bound is a separate, exact comparison.  A threshold k that is negative or not finite disables the
+// filter (-1: nothing is <= it).
+constexpr double kBandRel = 1.0 - 9.313225746154785e-10;  // 1 - 2^-30
+constexpr double kBandAbs = 9.094947017729282e-13;        // 2^-40
+__device__ __forceinline__ double band_clear(double k, double sig) {
+  return (k >= 0.0 && k < 1.0e150) ? (k * sig) * kBandRel : -1.0;
+}
+
 template <uint32_t ALGS>
 __device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t ns) {
   if (ALGS & FM_ALG_MA_ALL) {
@@ -148,9 +163,16 @@ __device__ __forceinline__ void finalize(State<ALGS> &s, const Rule &r, uint32_t
     s.ma_up = fma(r.k, sd, mean);
     double lo = fma(-r.k, sd, mean);
     s.ma_lo = lo < r.mlb ? r.mlb : lo;
+    // the prefix sums are done with: their registers carry the bounds cur_fast compares with, a side that the rule
+    // does not have pushed out to infinity (two comparisons per point, no rule bits)
+    s.s1 = (r.bound & 1u) ? s.ma_up : __longlong_as_double(0x7FF0000000000000ll);
+    s.s2 = (r.bound & 2u) ? s.ma_lo : __longlong_as_double(0xFFF0000000000000ll);
   }
   if (ALGS & FM_ALG_EWMA) s.esig = ns >= 2 ? sqrt(s.esse / (double)(ns - 1)) : 0.0;
   if (ALGS & FM_ALG_DES) s.dsig = ns >= 2 ? sqrt(s.dsse / (double)(ns - 1)) : 0.0;
+  // the residual sums are done with: their registers carry the inside-the-band thresholds of cur_fast from here on
+  if (ALGS & FM_ALG_EWMA) s.esse = band_clear(r.k, s.esig);
+  if (ALGS & FM_ALG_DES) s.dsse = band_clear(r.k, s.dsig);
 }
 
 // Per-thread form of the rule for the fast path: x < max(mlb, lo) is evaluated as
@@ -248,19 +270,24 @@ __device__ __forceinline__ void cur_fast(State<ALGS> &s, const FastRule &fr, dou
     else roll_advance<ALGS>(s, xd, q, lag, valid);
   }
   if (ALGS & FM_ALG_MA_ALL) {
-    // s.ma_lo already carries the clamp, so the plain comparison is the oracle's
-    if ((fr.up_on && xd > s.ma_up) || (fr.lo_on && xd < s.ma_lo)) mask[0] |= 1u << i;
+    // s.s1 / s.s2 = ma_up / ma_lo (which carries the clamp) or +-infinity for a side the rule does not have (finalize)
+    if ((xd > s.s1) | (xd < s.s2)) mask[0] |= 1u << i;
   }
+  const bool below = fr.lo_on & (xd < fr.mlb);  // the clamp of a lower band, shared by the forecast bands
   if (ALGS & FM_ALG_EWMA) {
-    const double f0 = s.es, up = fma(fr.k, s.esig, f0), lo = fma(fr.nk, s.esig, f0);
-    if (outside_fast(xd, up, lo, fr)) mask[1] |= 1u << i;
-    const double e = xd - f0;
+    const double f0 = s.es, e = xd - f0;
+    if (!(fabs(e) <= fma(-kBandAbs, fabs(f0) + fabs(xd), s.esse)) | below) {  // not provably inside (band_clear)
+      const double up = fma(fr.k, s.esig, f0), lo = fma(fr.nk, s.esig, f0);
+      if (outside_fast(xd, up, lo, fr)) mask[1] |= 1u << i;
+    }
     s.es = fma(alpha, e, s.es);
   }
   if (ALGS & FM_ALG_DES) {
-    const double f0 = s.dl + s.db, up = fma(fr.k, s.dsig, f0), lo = fma(fr.nk, s.dsig, f0);
-    if (outside_fast(xd, up, lo, fr)) mask[2] |= 1u << i;
-    const double e = xd - f0;
+    const double f0 = s.dl + s.db, e = xd - f0;
+    if (!(fabs(e) <= fma(-kBandAbs, fabs(f0) + fabs(xd), s.dsse)) | below) {
+      const double up = fma(fr.k, s.dsig, f0), lo = fma(fr.nk, s.dsig, f0);
+      if (outside_fast(xd, up, lo, fr)) mask[2] |= 1u << i;
+    }
     s.dl = fma(alpha, e, f0);
     s.db = fma(ab, e, s.db);
   }
@@ -318,7 +345,7 @@ __device__ __forceinline__ void cur_update(State<ALGS> &s, const Rule &r, double
 // Two 8-warp blocks per SM need at most 128 registers; the kernels with three or four scorers where ptxas would take a
 // few more (and halve the occupancy) are held to that.  The others are left alone: told "two blocks", ptxas spends the
 // allowance (91 -> 126 registers for EWMA + DES), which costs the 6-warp blocks of small batches their third block.
-constexpr int band_min_blocks(uint32_t algs) { return (algs == 7u || algs == 14u || algs == 15u) ? 2 : 0; }  // 0: no statement
+constexpr int band_min_blocks(uint32_t algs) { return (algs == 7u || algs == 11u || algs == 14u || algs == 15u) ? 2 : 0; }  // 0: no statement
 
 template <uint32_t ALGS, int MODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_band(DevBatch b, const DevParams *__restrict__ dp,
