@@ -740,6 +740,41 @@ def test_mann_whitney_search_kernel_extremes(ctx, oracle):
     b.free()
 
 
+@pytest.mark.parametrize("alg", [abi.ALG_EWMA, abi.ALG_DES, abi.ALG_MA_ALL])
+def test_forecast_band_filter_points_on_the_edge(ctx, oracle, alg):
+    """In chunks that lie inside the current window k_band proves most points inside their EWMA / DES band from
+    |x - forecast| alone and takes the oracle's arithmetic for the rest (fm_band.cu band_clear).  Here the 41st current
+    point of every unit -- inside such a chunk -- is moved ONTO its band edge as the oracle computes it (the float
+    next to it on either side, the upper or the lower edge), for noisy, integer-valued, offset and nearly constant
+    series and tight to loose thresholds: counts and first indices must stay bit-identical."""
+    rng = np.random.default_rng(300 + alg)
+    n, n_model, n_cur, j = 600, 96, 96, 40
+    kinds = [lambda m: rng.normal(100, 5, m), lambda m: np.round(rng.normal(50, 2, m)), lambda m: 1e6 + rng.normal(0, 3, m),
+             lambda m: rng.normal(0, 1, m) * 1e-3, lambda m: 7.0 + (rng.random(m) < 0.05) * 0.5]
+    base = [kinds[i % len(kinds)](n_model + n_cur).astype(np.float32) for i in range(n)]
+    sid, mts = np.arange(n) // 6, rng.integers(0, 8, n)
+    for k, bound in ((0.5, abi.BOUND_BOTH), (2.0, abi.BOUND_UPPER), (3.0, abi.BOUND_BOTH), (1.5, abi.BOUND_LOWER)):
+        p = full_params(oracle, abi.ALG_MA_ALL | abi.ALG_EWMA | abi.ALG_DES, abi.PW_NONE)
+        for mt in range(9):
+            p.rules[mt].threshold, p.rules[mt].bound, p.rules[mt].min_lower_bound = k, bound, (0.0 if mt % 2 else -1e30)
+        h = abi.HostCsr.from_units([([], z[:n_model], z[n_model:]) for z in base], sid, mts)
+        p.band_algorithm = alg
+        _, up, lo = oracle.score(h, p, want_bands=True)
+        p.band_algorithm = 0
+        moved = []
+        for i, z in enumerate(base):
+            o = int(h.offsets[i]) + n_model + j
+            edge = np.float32(up[o] if i % 2 == 0 else lo[o])
+            z = z.copy()
+            z[n_model + j] = (edge, np.nextafter(edge, np.float32(np.inf)), np.nextafter(edge, np.float32(-np.inf)))[(i // 2) % 3]
+            moved.append(z)
+        b = ctx.batch_from_units([([], z[:n_model], z[n_model:]) for z in moved], service_id=sid, metric_type=mts)
+        got, _ = check_batch(ctx, oracle, b, p)
+        a = {abi.ALG_MA_ALL: 0, abi.ALG_EWMA: 2, abi.ALG_DES: 3}[alg]
+        assert (got["n_anom"][:, a] > 0).any()
+        b.free()
+
+
 @pytest.mark.parametrize("window", [1, 2, 7, 30, 32, 33, 100])
 def test_rolling_band_filter_adversarial(ctx, oracle, window):
     """The rolling band decides most points with a division-free filter and the rest with the oracle's exact
