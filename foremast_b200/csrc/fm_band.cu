@@ -366,7 +366,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_
   constexpr int kSlots = ring_slots(ALGS);
   const int wpb = (int)(blockDim.x >> 5), kRingB = ring_bytes(ALGS, wpb);  // warps per block is a launch-time choice
   float *const s_ring = reinterpret_cast<float *>(smem_raw) + warp * (kSlots * 32 * kRowWords);
-  int64_t *const s_off = reinterpret_cast<int64_t *>(smem_raw + kRingB) + warp * 32;
+  // per row: the address of the unit's first sample (as a number: the staging adds the chunk's byte offset to it) ...
+  unsigned long long *const s_src = reinterpret_cast<unsigned long long *>(smem_raw + kRingB) + warp * 32;
   uint32_t *const s_len = reinterpret_cast<uint32_t *>(smem_raw + kRingB + wpb * 32 * 8) + warp * 32;
   float *const s_lo = reinterpret_cast<float *>(smem_raw + kRingB + wpb * 32 * (8 + 4)) + warp * (32 * kRowWords);  // MODE 1 only
   const uint64_t gid = ((uint64_t)blockIdx.x * wpb + warp) * 32 + lane;
@@ -430,7 +431,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_
   const uint32_t w_uniform = dp->ma_window;
 
   // ---- staging set-up
-  s_off[lane] = off;
+  s_src[lane] = (unsigned long long)reinterpret_cast<uintptr_t>(b.values + off);
   s_len[lane] = (active && ALGS) ? ((ntot + 3u) & ~3u) : 0u;   // inactive units are not even read
   __syncwarp();
   // with no band algorithm selected the kernel only resolves statuses: nothing is staged
@@ -440,12 +441,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_
   auto issue = [&](uint32_t ch) {
     if (ch < nchunks) {
       float *dst = s_ring + (ch % kSlots) * (32 * kRowWords);
+      const uint32_t pos = ch * kChunk + col4 * 4;
 #pragma unroll
       for (int rr = 0; rr < 8; ++rr) {
         const unsigned row = rr * 4 + row_sub;
-        const uint32_t pos = ch * kChunk + col4 * 4;
         if (pos < s_len[row])
-          cp_async16(dst + row * kRowWords + col4 * 4, b.values + s_off[row] + pos);
+          cp_async16(dst + row * kRowWords + col4 * 4, reinterpret_cast<const float *>((uintptr_t)(s_src[row] + 4ull * pos)));
       }
     }
     cp_async_commit();
@@ -533,7 +534,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_
       for (int rr = 0; rr < 8; ++rr) {
         const unsigned rw = rr * 4 + row_sub;
         if ((rows_ok >> rw) & 1u) {
-          const int64_t at = s_off[rw] + cs + col4 * 4;  // unit start and chunk start are multiples of 4: 16 B aligned
+          const int64_t at = (int64_t)((s_src[rw] - (unsigned long long)reinterpret_cast<uintptr_t>(b.values)) >> 2) + cs + col4 * 4;  // unit start and chunk start are multiples of 4: 16 B aligned
           *reinterpret_cast<float4 *>(band_up + at) = *reinterpret_cast<const float4 *>(ups + rw * kRowWords + col4 * 4);
           *reinterpret_cast<float4 *>(band_lo + at) = *reinterpret_cast<const float4 *>(s_lo + rw * kRowWords + col4 * 4);
         }
