@@ -442,11 +442,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, band_min_blocks(ALGS)) k_
     if (ch < nchunks) {
       float *dst = s_ring + (ch % kSlots) * (32 * kRowWords);
       const uint32_t pos = ch * kChunk + col4 * 4;
+      uint32_t len[8];
+      unsigned long long src[8];
+#pragma unroll
+      for (int rr = 0; rr < 8; ++rr) { len[rr] = s_len[rr * 4 + row_sub]; src[rr] = s_src[rr * 4 + row_sub]; }
 #pragma unroll
       for (int rr = 0; rr < 8; ++rr) {
         const unsigned row = rr * 4 + row_sub;
-        if (pos < s_len[row])
-          cp_async16(dst + row * kRowWords + col4 * 4, reinterpret_cast<const float *>((uintptr_t)(s_src[row] + 4ull * pos)));
+        if (pos < len[rr])
+          cp_async16(dst + row * kRowWords + col4 * 4, reinterpret_cast<const float *>((uintptr_t)(src[rr] + 4ull * pos)));
       }
     }
     cp_async_commit();
