@@ -329,7 +329,7 @@ def run_ours(args):
         for _ in range(200):
             ctx.score_host(h0, q, 1)
         other["cfg0_single_canary_job_5_series"] = {"us_per_call": (time.perf_counter() - t0) / 200 * 1e6,
-                                                    "note": "fm_score_host small-job path: one upload, one clear, the launches, one download; no allocation"}
+                                                    "note": "fm_score_host small-job path: one upload, four launches, one download (the clear rides behind the previous call); no allocation"}
         # cfg0's job shape at scale: what batching jobs buys (BrainWorker.process_many puts every open job document
         # of a cycle into one batch).  200 000 canary jobs x 5 series x (60 + 30) points, MA band + Mann-Whitney U.
         ms, info = timed(lambda: ctx.batch_synth(1_000_000, 0, 60, 30, units_per_service=5, n_metric_types=5,
